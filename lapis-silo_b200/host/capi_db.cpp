@@ -1,0 +1,72 @@
+// C entry points for building / inspecting the host Database (used through ctypes by tests,
+// bench.py and __graft_entry__; a C++ host links the headers directly).
+#include "builder.hpp"
+#include "capi_common.hpp"
+
+using namespace silo;
+
+extern "C" {
+
+const char* silo_last_error() { return capi::lastError().c_str(); }
+void silo_free(void* p) { free(p); }
+
+void* silo_db_build_from_dir(const char* dir) {
+   Database* db = nullptr;
+   capi::guarded([&] { db = builder::buildDatabaseFromDirectory(dir).release(); });
+   return db;
+}
+void silo_db_free(void* db) { delete static_cast<Database*>(db); }
+uint32_t silo_db_partition_count(const void* db) { return static_cast<uint32_t>(static_cast<const Database*>(db)->partitions.size()); }
+uint32_t silo_db_partition_rows(const void* db, uint32_t p) { return static_cast<const Database*>(db)->partitions.at(p)->sequence_count; }
+
+// Mirrors Database::getDatabaseInfo / detailedDatabaseInfo (src/silo/database.cpp:122-146,239-305)
+char* silo_db_info_json(const void* db_) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      const auto& db = *static_cast<const Database*>(db_);
+      uint64_t total_size = 0, n_bitmaps_size = 0, sequence_count = 0;
+      json::Value sequences = json::Value::object();
+      std::map<std::string, std::array<uint64_t, 8>> per_sequence;  // arr, arr_values, run, run_values, bitset, bitset_values, portable, run_bytes
+      for (const auto& part : db.partitions) {
+         sequence_count += part->sequence_count;
+         for (const auto& [name, store] : part->nuc_sequences) {
+            auto& st = per_sequence[name];
+            for (const auto& bm : store.bitmaps) {
+               total_size += bm.nonPortableSizeInBytes();
+               st[6] += bm.portableSizeInBytes();
+               for (const auto& c : bm.containers) {
+                  if (c.kind == roaring::ARRAY) { st[0]++; st[1] += c.card; }
+                  else if (c.kind == roaring::RUN) { st[2]++; st[3] += c.card; st[7] += 2 + 4 * c.runCount(); }
+                  else { st[4]++; st[5] += c.card; }
+               }
+            }
+            for (const auto& bm : store.missing_symbol_bitmaps) n_bitmaps_size += bm.nonPortableSizeInBytes();
+         }
+      }
+      for (const auto& [name, st] : per_sequence) {
+         json::Value s = json::Value::object();
+         s.set("numberOfArrayContainers", json::Value::integer(st[0]));
+         s.set("numberOfValuesStoredInArrayContainers", json::Value::integer(st[1]));
+         s.set("numberOfRunContainers", json::Value::integer(st[2]));
+         s.set("numberOfValuesStoredInRunContainers", json::Value::integer(st[3]));
+         s.set("numberOfBitsetContainers", json::Value::integer(st[4]));
+         s.set("numberOfValuesStoredInBitsetContainers", json::Value::integer(st[5]));
+         s.set("totalBitmapSizeComputed", json::Value::integer(st[6]));
+         s.set("totalBitmapSizeArrayContainers", json::Value::integer(2 * st[1]));
+         sequences.set(name, std::move(s));
+      }
+      json::Value info = json::Value::object();
+      info.set("sequenceCount", json::Value::integer(sequence_count));
+      info.set("totalSize", json::Value::integer(total_size));
+      info.set("nBitmapsSize", json::Value::integer(n_bitmaps_size));
+      info.set("numberOfPartitions", json::Value::integer(db.partitions.size()));
+      json::Value rows = json::Value::array();
+      for (const auto& part : db.partitions) rows.arr.push_back(json::Value::integer(part->sequence_count));
+      info.set("partitionRows", std::move(rows));
+      info.set("sequences", std::move(sequences));
+      out = capi::dupString(info.dump());
+   });
+   return out;
+}
+
+}  // extern "C"

@@ -1,0 +1,373 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_roaring.hpp). CPU restatement of the reference's
+// query hot path: Operator::evaluate for all 11 operators, Mutations<SymbolType>::execute,
+// Aggregated (count) and QueryEngine::executeQuery. Each function cites the reference lines it
+// follows. Parity: PINNED — against the operator known-answer tests ported from
+// src/silo/query_engine/operators/*.test.cpp, the 63 hot-path e2e fixtures of
+// endToEndTests/test/queries/*.json on testBaseData/exampleDataset, and the size / container
+// goldens of src/silo/database.test.cpp:74-111 (tests/test_oracle_*.py).
+#pragma once
+#include <atomic>
+#include <thread>
+
+#include "../lapis-silo_b200/host/query.hpp"
+#include "oracle_roaring.hpp"
+
+namespace oracle {
+
+using namespace silo;
+using silo::operators::Operator;
+
+// include/silo/query_engine/operator_result.h:9-32: owned-or-borrowed bitmap, copy on first write
+struct OperatorResult {
+   const Bitmap* borrowed = nullptr;
+   Bitmap owned;
+   bool is_owned = true;
+   OperatorResult() = default;
+   explicit OperatorResult(const Bitmap* b) : borrowed(b), is_owned(false) {}
+   explicit OperatorResult(Bitmap&& b) : owned(std::move(b)), is_owned(true) {}
+   const Bitmap& get() const { return is_owned ? owned : *borrowed; }
+   Bitmap& mut() {  // operator_result.cpp:40-54
+      if (!is_owned) { owned = *borrowed; is_owned = true; borrowed = nullptr; }
+      return owned;
+   }
+   bool isMutable() const { return is_owned; }
+};
+
+OperatorResult evaluate(const Operator& op);
+
+inline OperatorResult evaluateIntersection(const Operator& op) {  // intersection.cpp:76-127
+   std::vector<OperatorResult> children, negated;
+   for (const auto& c : op.children) children.push_back(evaluate(*c));
+   for (const auto& c : op.negated_children) negated.push_back(evaluate(*c));
+   std::sort(children.begin(), children.end(), [](const OperatorResult& a, const OperatorResult& b) { return a.get().cardinality() < b.get().cardinality(); });
+   std::sort(negated.begin(), negated.end(), [](const OperatorResult& a, const OperatorResult& b) { return a.get().cardinality() > b.get().cardinality(); });
+   if (children.size() == 1) {
+      OperatorResult result = std::move(children[0]);
+      for (auto& n : negated) result.mut() = bitmapAndNot(result.get(), n.get());
+      return result;
+   }
+   OperatorResult result(bitmapAnd(children[0].get(), children[1].get()));  // intersectTwo (:62-74)
+   for (size_t i = 2; i < children.size(); ++i) result.owned = bitmapAnd(result.owned, children[i].get());
+   for (auto& n : negated) result.owned = bitmapAndNot(result.owned, n.get());
+   return result;
+}
+
+inline OperatorResult evaluateThreshold(const Operator& op) {  // threshold.cpp:64-138
+   const uint32_t dp_table_size = op.match_exactly ? op.number_of_matchers + 1 : op.number_of_matchers;
+   std::vector<Bitmap> T(dp_table_size);
+   if (op.children.empty()) {
+      T[0] = evaluate(*op.negated_children[0]).get();
+      T[0].flip(0, op.row_count);
+   } else {
+      T[0] = evaluate(*op.children[0]).get();
+   }
+   const int max_table_index = static_cast<int>(dp_table_size - 1);
+   const int non_negated_child_count = static_cast<int>(op.children.size());
+   const int negated_child_count = static_cast<int>(op.negated_children.size());
+   const int n = static_cast<int>(op.number_of_matchers);
+   const int k = non_negated_child_count + negated_child_count;
+   for (int i = 1; i < non_negated_child_count; ++i) {
+      auto bitmap = evaluate(*op.children[i]);
+      for (int j = std::min(max_table_index, i); j > std::max(0, n - k + i - 1); --j) {
+         T[j] = bitmapOr(T[j], bitmapAnd(T[j - 1], bitmap.get()));
+      }
+      if (k - i > n - 1) T[0] = bitmapOr(T[0], bitmap.get());
+   }
+   const int took_first_offset = op.children.empty() ? 1 : 0;
+   for (int local_i = took_first_offset; local_i < negated_child_count; ++local_i) {
+      auto bitmap = evaluate(*op.negated_children[local_i]);
+      const int i = local_i + non_negated_child_count;
+      for (int j = std::min(max_table_index, i); j > std::max(0, n - k + i - 1); --j) {
+         T[j] = bitmapOr(T[j], bitmapAndNot(T[j - 1], bitmap.get()));
+      }
+      if (k - i > n - 1) {
+         bitmap.mut().flip(0, op.row_count);
+         T[0] = bitmapOr(T[0], bitmap.get());
+      }
+   }
+   if (op.match_exactly) {
+      T[n - 1] = bitmapAndNot(T[n - 1], T[n]);
+      return OperatorResult(std::move(T[n - 1]));
+   }
+   return OperatorResult(std::move(T.back()));
+}
+
+inline OperatorResult evaluate(const Operator& op) {
+   switch (op.type()) {
+      case operators::EMPTY: return OperatorResult();                         // empty.cpp:24-26
+      case operators::FULL: {                                                 // full.cpp:24-28
+         OperatorResult r;
+         r.owned.addRange(0, op.row_count);
+         return r;
+      }
+      case operators::INDEX_SCAN: return OperatorResult(op.bitmap);           // index_scan.cpp:28-30
+      case operators::INTERSECTION: return evaluateIntersection(op);
+      case operators::COMPLEMENT: {                                           // complement.cpp:50-54
+         auto r = evaluate(*op.children[0]);
+         r.mut().flip(0, op.row_count);
+         return r;
+      }
+      case operators::RANGE_SELECTION: {                                      // range_selection.cpp:42-48
+         OperatorResult r;
+         for (const auto& range : op.ranges) r.owned.addRange(range.start, range.end);
+         return r;
+      }
+      case operators::SELECTION: {                                            // selection.cpp:92-109
+         OperatorResult r;
+         auto matches = [&](uint32_t row) { for (const auto& p : op.predicates) if (!p.match(row)) return false; return true; };
+         if (!op.children.empty()) {
+            auto child = evaluate(*op.children[0]);
+            child.get().forEach([&](uint32_t row) { if (matches(row)) r.owned.add(row); });
+         } else {
+            for (uint32_t row = 0; row < op.row_count; ++row) if (matches(row)) r.owned.add(row);
+         }
+         return r;
+      }
+      case operators::BITMAP_SELECTION: {                                     // bitmap_selection.cpp:33-52
+         OperatorResult r;
+         const auto& bitmaps = op.store->missing_symbol_bitmaps;
+         for (uint32_t i = 0; i < op.row_count; ++i) if (bitmaps[i].contains(op.value) == op.contains) r.owned.add(i);
+         return r;
+      }
+      case operators::THRESHOLD: return evaluateThreshold(op);
+      case operators::UNION: {                                                // union.cpp:35-45
+         std::vector<OperatorResult> results;
+         for (const auto& c : op.children) results.push_back(evaluate(*c));
+         std::vector<const Bitmap*> ptrs;
+         for (const auto& r : results) ptrs.push_back(&r.get());
+         return OperatorResult(fastUnion(ptrs));
+      }
+      case operators::BITMAP_PRODUCER: return OperatorResult(op.producer());  // bitmap_producer.cpp:25-27
+   }
+   throw std::runtime_error("unknown operator type");
+}
+
+// ---- Mutations (actions/mutations.cpp) ---------------------------------------------------------
+
+struct FilterAndStore { const Bitmap* filter; const SequenceStorePartition* store; };
+struct PrefilteredBitmaps { std::vector<FilterAndStore> bitmaps, full_bitmaps; };
+
+// mutations.cpp:36-63
+inline std::map<std::string, PrefilteredBitmaps> preFilterBitmaps(const Database& db, int alphabet_id, std::vector<OperatorResult>& filters) {
+   std::map<std::string, PrefilteredBitmaps> out;
+   for (size_t i = 0; i < db.partitions.size(); ++i) {
+      const DatabasePartition& part = *db.partitions[i];
+      OperatorResult& filter = filters[i];
+      const uint64_t cardinality = filter.get().cardinality();
+      if (cardinality == 0) continue;
+      if (cardinality == part.sequence_count) {
+         for (const auto& [name, store] : part.getSequenceStores(alphabet_id)) out[name].full_bitmaps.push_back({&filter.get(), &store});
+      } else {
+         if (filter.isMutable()) filter.owned.runOptimize();
+         for (const auto& [name, store] : part.getSequenceStores(alphabet_id)) out[name].bitmaps.push_back({&filter.get(), &store});
+      }
+   }
+   return out;
+}
+
+// mutations.cpp:66-98 (faithful: O(|F|) contains() calls per position for the deleted symbol)
+inline void addPositionForMixedBitmaps(uint32_t pos, const PrefilteredBitmaps& pre, uint32_t* counts, size_t length, const Alphabet& alphabet) {
+   for (const auto& [filter, store] : pre.bitmaps) {
+      for (Symbol symbol : alphabet.iteration_order) {
+         if (store->isSymbolDeleted(pos, symbol)) {
+            counts[symbol * length + pos] += static_cast<uint32_t>(filter->cardinality());
+            filter->forEach([&](uint32_t idx) { if (store->missing_symbol_bitmaps[idx].contains(pos)) counts[symbol * length + pos] -= 1; });
+            continue;
+         }
+         const uint32_t symbol_count = static_cast<uint32_t>(
+            store->isSymbolFlipped(pos, symbol) ? andnotCardinality(*filter, *store->getBitmap(pos, symbol)) : andCardinality(*filter, *store->getBitmap(pos, symbol)));
+         counts[symbol * length + pos] += symbol_count;
+         const int8_t deleted = store->deleted[pos];
+         if (deleted >= 0 && symbol != static_cast<Symbol>(deleted)) counts[size_t(deleted) * length + pos] -= symbol_count;
+      }
+   }
+}
+// mutations.cpp:101-136
+inline void addPositionForFullBitmaps(uint32_t pos, const PrefilteredBitmaps& pre, uint32_t* counts, size_t length, const Alphabet& alphabet) {
+   for (const auto& [filter, store] : pre.full_bitmaps) {
+      for (Symbol symbol : alphabet.iteration_order) {
+         if (store->isSymbolDeleted(pos, symbol)) {
+            counts[symbol * length + pos] += store->sequence_count;
+            for (const Bitmap& n_bitmap : store->missing_symbol_bitmaps) if (n_bitmap.contains(pos)) counts[symbol * length + pos] -= 1;
+            continue;
+         }
+         const uint32_t card = static_cast<uint32_t>(store->getBitmap(pos, symbol)->cardinality());
+         const uint32_t symbol_count = store->isSymbolFlipped(pos, symbol) ? store->sequence_count - card : card;
+         counts[symbol * length + pos] += symbol_count;
+         const int8_t deleted = store->deleted[pos];
+         if (deleted >= 0 && symbol != static_cast<Symbol>(deleted)) counts[size_t(deleted) * length + pos] -= card;
+      }
+   }
+}
+
+// "fast mode": same sums, but the per-position missing counts of the deleted symbol come from a
+// difference array over the missing runs of the filtered rows instead of
+// |F| x L contains() calls. Must equal the faithful mode (tests/test_oracle_synthetic.py).
+inline void addStoreFast(const FilterAndStore& fs, bool full, uint32_t* counts, size_t length, const Alphabet& alphabet) {
+   const Bitmap& filter = *fs.filter;
+   const SequenceStorePartition& store = *fs.store;
+   std::vector<int32_t> diff(length + 1, 0);
+   auto addRow = [&](uint32_t idx) {
+      for (const auto& c : store.missing_symbol_bitmaps[idx].containers) {
+         const uint32_t base = static_cast<uint32_t>(c.key) << 16;
+         if (c.kind == RUN) {
+            for (uint32_t r = 0; r < c.runCount(); ++r) { diff[base + c.data[2 * r]] += 1; diff[base + c.data[2 * r] + c.data[2 * r + 1] + 1] -= 1; }
+         } else c.forEach([&](uint32_t v) { diff[v] += 1; diff[v + 1] -= 1; });
+      }
+   };
+   uint32_t filter_card;
+   if (full) { filter_card = store.sequence_count; for (uint32_t idx = 0; idx < store.sequence_count; ++idx) addRow(idx); }
+   else { filter_card = static_cast<uint32_t>(filter.cardinality()); filter.forEach(addRow); }
+   int32_t running = 0;
+   for (uint32_t pos = 0; pos < length; ++pos) {
+      running += diff[pos];
+      for (Symbol symbol : alphabet.iteration_order) {
+         if (store.isSymbolDeleted(pos, symbol)) { counts[symbol * length + pos] += filter_card - static_cast<uint32_t>(running); continue; }
+         const Bitmap& bm = *store.getBitmap(pos, symbol);
+         if (bm.isEmpty() && !store.isSymbolFlipped(pos, symbol)) continue;
+         const uint32_t card = static_cast<uint32_t>(full ? bm.cardinality() : andCardinality(filter, bm));
+         const uint32_t symbol_count = store.isSymbolFlipped(pos, symbol) ? filter_card - card : card;
+         counts[symbol * length + pos] += symbol_count;
+         const int8_t deleted = store.deleted[pos];
+         if (deleted >= 0 && symbol != static_cast<Symbol>(deleted)) counts[size_t(deleted) * length + pos] -= full ? card : symbol_count;
+      }
+   }
+}
+
+// mutations.cpp:139-164: positions split in chunks of 300 over a thread pool (TBB in the reference)
+inline std::vector<uint32_t> calculateMutationsPerPosition(const Alphabet& alphabet, size_t length, const PrefilteredBitmaps& pre, bool faithful, unsigned n_threads) {
+   std::vector<uint32_t> counts(size_t(alphabet.count) * length, 0);
+   if (n_threads == 0) n_threads = std::max(1u, std::thread::hardware_concurrency());
+   if (faithful) {
+      constexpr uint32_t POSITIONS_PER_PROCESS = 300;
+      std::atomic<uint32_t> next{0};
+      auto worker = [&] {
+         while (true) {
+            const uint32_t begin = next.fetch_add(POSITIONS_PER_PROCESS);
+            if (begin >= length) break;
+            const uint32_t end = std::min<uint32_t>(begin + POSITIONS_PER_PROCESS, static_cast<uint32_t>(length));
+            for (uint32_t pos = begin; pos < end; ++pos) {
+               addPositionForMixedBitmaps(pos, pre, counts.data(), length, alphabet);
+               addPositionForFullBitmaps(pos, pre, counts.data(), length, alphabet);
+            }
+         }
+      };
+      std::vector<std::thread> threads;
+      for (unsigned t = 1; t < n_threads; ++t) threads.emplace_back(worker);
+      worker();
+      for (auto& t : threads) t.join();
+   } else {
+      // fast mode: one private table per worker, stores distributed over workers, summed at the end
+      std::vector<std::pair<FilterAndStore, bool>> work;
+      for (const auto& fs : pre.bitmaps) work.push_back({fs, false});
+      for (const auto& fs : pre.full_bitmaps) work.push_back({fs, true});
+      std::atomic<size_t> next{0};
+      std::vector<std::vector<uint32_t>> partial(std::min<size_t>(n_threads, std::max<size_t>(1, work.size())));
+      auto worker = [&](size_t t) {
+         partial[t].assign(counts.size(), 0);
+         while (true) {
+            const size_t w = next.fetch_add(1);
+            if (w >= work.size()) break;
+            addStoreFast(work[w].first, work[w].second, partial[t].data(), length, alphabet);
+         }
+      };
+      std::vector<std::thread> threads;
+      for (size_t t = 1; t < partial.size(); ++t) threads.emplace_back(worker, t);
+      worker(0);
+      for (auto& t : threads) t.join();
+      for (const auto& p : partial) for (size_t k = 0; k < counts.size(); ++k) counts[k] += p[k];
+   }
+   return counts;
+}
+
+// mutations.cpp:185-232
+inline void addMutationsToOutput(const std::string& sequence_name, const Alphabet& alphabet, const std::vector<Symbol>& reference_sequence,
+                                 const std::vector<uint32_t>& counts, double min_proportion, std::vector<QueryResultEntry>& output) {
+   const size_t sequence_length = reference_sequence.size();
+   for (size_t pos = 0; pos < sequence_length; ++pos) {
+      uint32_t total = 0;
+      for (const Symbol symbol : alphabet.valid_mutation_symbols) total += counts[symbol * sequence_length + pos];
+      if (total == 0) continue;
+      const auto threshold_count = min_proportion == 0 ? 0 : static_cast<uint32_t>(std::ceil(static_cast<double>(total) * min_proportion) - 1);
+      const Symbol symbol_in_reference_genome = reference_sequence.at(pos);
+      for (const Symbol symbol : alphabet.valid_mutation_symbols) {
+         if (symbol_in_reference_genome != symbol) {
+            const uint32_t count = counts[symbol * sequence_length + pos];
+            if (count > threshold_count) {
+               const double proportion = static_cast<double>(count) / static_cast<double>(total);
+               QueryResultEntry entry;
+               entry.fields["mutation"] = std::string(1, alphabet.symbolToChar(symbol_in_reference_genome)) + std::to_string(pos + 1) + alphabet.symbolToChar(symbol);
+               entry.fields["sequenceName"] = sequence_name;
+               entry.fields["proportion"] = proportion;
+               entry.fields["count"] = static_cast<int32_t>(count);
+               output.push_back(std::move(entry));
+            }
+         }
+      }
+   }
+}
+
+struct Options { bool faithful = true; unsigned threads = 0; };
+
+// query_engine.cpp:40-49: serial compile + evaluate per partition
+inline std::vector<OperatorResult> evaluateFilters(const Database& db, const filter::Expression& filter_expression,
+                                                   std::vector<operators::OperatorPtr>* keep_alive) {
+   std::vector<OperatorResult> partition_filters;
+   for (const auto& part : db.partitions) {
+      auto op = filter_expression.compile(db, *part, filter::AmbiguityMode::NONE);
+      partition_filters.push_back(evaluate(*op));
+      keep_alive->push_back(std::move(op));  // BitmapSelection / IndexScan results may borrow from the tree's sources
+   }
+   return partition_filters;
+}
+
+// mutations.cpp:235-272; returns per sequence name the full [Σ][L] table through `tables` if given
+inline QueryResult executeMutations(const Database& db, const Action& action, std::vector<OperatorResult>& filters, const Options& options,
+                                    std::map<std::string, std::vector<uint32_t>>* tables = nullptr) {
+   const int alphabet_id = action.alphabetId();
+   const Alphabet& alphabet = alphabetById(alphabet_id);
+   const auto& references = db.getReferences(alphabet_id);
+   std::vector<std::string> names;
+   for (const auto& name : action.sequence_names) {
+      CHECK_SILO_QUERY(references.count(name), "Database does not contain the " + std::string(alphabet.name_lower) + " sequence with name: '" + name + "'")
+      names.push_back(name);
+   }
+   if (action.sequence_names.empty()) for (const auto& [name, _] : references) names.push_back(name);
+   auto pre = preFilterBitmaps(db, alphabet_id, filters);
+   QueryResult result;
+   for (const auto& name : names) {
+      const auto& reference = references.at(name);
+      auto it = pre.find(name);
+      if (it == pre.end()) continue;
+      auto counts = calculateMutationsPerPosition(alphabet, reference.size(), it->second, options.faithful, options.threads);
+      addMutationsToOutput(name, alphabet, reference, counts, action.min_proportion, result.query_result);
+      if (tables) (*tables)[name] = std::move(counts);
+   }
+   return result;
+}
+
+// aggregated.cpp:58-66
+inline QueryResult aggregateWithoutGrouping(const std::vector<OperatorResult>& filters) {
+   uint32_t count = 0;
+   for (const auto& f : filters) count += static_cast<uint32_t>(f.get().cardinality());
+   QueryResultEntry entry;
+   entry.fields["count"] = static_cast<int32_t>(count);
+   return QueryResult{{entry}};
+}
+
+// query_engine.cpp:30-68
+inline QueryResult executeQuery(const Database& db, const std::string& query_string, const Options& options,
+                                std::map<std::string, std::vector<uint32_t>>* tables = nullptr) {
+   Query query = parseQuery(query_string);
+   std::vector<operators::OperatorPtr> trees;
+   std::vector<OperatorResult> filters = evaluateFilters(db, *query.filter, &trees);
+   return query.action.executeAndOrder([&]() -> QueryResult {
+      if (query.action.type == ActionType::AGGREGATED) {
+         if (!query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+         return aggregateWithoutGrouping(filters);
+      }
+      return executeMutations(db, query.action, filters, options, tables);
+   });
+}
+
+}  // namespace oracle
