@@ -1,0 +1,156 @@
+/* silo_b200.h — C ABI of the B200 query hot path (libsilo_b200.so).
+ *
+ * The reference (pflanze/LAPIS-SILO) has no plugin / FFI layer; its hot path sits behind two C++
+ * virtuals that are called from exactly one place:
+ *     Operator::evaluate()          include/silo/query_engine/operators/operator.h:32
+ *                                   (called at src/silo/query_engine/query_engine.cpp:48)
+ *     Action::execute(db, filters)  include/silo/query_engine/actions/action.h:37-40
+ *                                   (called through executeAndOrder, query_engine.cpp:60)
+ * This header is what a binding for those two call sites links against. Plain pointers and sizes
+ * only; no C++ or torch types; every function returns 0 on success, non-zero on failure with the
+ * text available from sb_last_error() (thread-local). A failure never aborts the process: the host
+ * turns it into an exception -> HTTP 500 (src/silo_api/query_handler.cpp:47-73).
+ *
+ * Threading: calls on one sb_db are serialised internally (one CUDA stream per sb_db); create /
+ * finalize / free are exclusive (the reference swaps databases under a unique lock,
+ * src/silo_api/database_mutex.cpp:15-18).
+ * There is no CPU fallback: every entry point needs a CUDA device and fails loudly without one.
+ */
+#ifndef SILO_B200_H
+#define SILO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sb_db sb_db;         /* device-resident index of the partitions owned by this GPU   */
+typedef struct sb_result sb_result; /* filter result of one partition: dense device bitset + |F|   */
+
+/* ---- lifecycle ------------------------------------------------------------------------------ */
+const char* sb_last_error(void);
+int sb_device_count(int* n);
+/* One sb_db per process+GPU. `n_partitions` = number of DatabasePartitions held by THIS db
+ * (include/silo/database.h:41). Replaces the in-memory Database for the hot path; built where
+ * Database::loadDatabaseState finishes (src/silo/database.cpp:480-560). */
+int sb_db_create(int device, uint32_t n_partitions, sb_db** out);
+int sb_db_free(sb_db* db);
+
+/* ---- ingest (before sb_db_finalize) ------------------------------------------------------------ */
+/* A roaring bitmap exactly as roaring::Roaring::write(buf, portable=true) emits it
+ * (include/silo/roaring/roaring_serialize.h:23-28). len == 0 means the empty bitmap.
+ * Used for the metadata index bitmaps that IndexScan leaves borrow:
+ * PangoLineageColumnPartition::indexed_values / indexed_sublineage_values
+ * (include/silo/storage/column/pango_lineage_column.h:37-39) and
+ * IndexedStringColumnPartition::indexed_values (indexed_string_column.h:34-36). */
+int sb_bitmap_add_portable(sb_db* db, uint32_t partition, const void* bytes, size_t len, uint32_t* bitmap_id);
+
+/* One SequenceStorePartition<S> (include/silo/storage/sequence_store.h:34-88):
+ *   alphabet   0 nucleotide (16 symbols), 1 amino acid (25 symbols); symbol = enum value
+ *   length     number of positions L;  n_rows = sequence_count
+ *   blob/slot_off   concatenated portable bitmaps; bitmap of (pos, sym) = bytes
+ *                   [slot_off[pos*S+sym], slot_off[pos*S+sym+1])   (Position::bitmaps, position.h:35)
+ *   flipped / deleted   per position symbol or -1 (position.h:36-37); both are honoured
+ *   missing_blob/missing_off   per row: portable bitmap over POSITIONS (sequence_store.h:55)
+ * Stores with the same `name` in different partitions form one logical sequence. */
+int sb_store_add(sb_db* db, uint32_t partition, const char* name, int alphabet, uint32_t length, uint32_t n_rows,
+                 const uint8_t* blob, const uint64_t* slot_off, const int8_t* flipped, const int8_t* deleted,
+                 const uint8_t* missing_blob, const uint64_t* missing_off, uint32_t* store_id);
+
+/* A metadata column vector borrowed by Selection predicates (operators/selection.h:33).
+ * dtype: 0 int32 (IntColumnPartition), 1 float64 (FloatColumnPartition), 2 uint32 date (DateColumnPartition). */
+int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, uint32_t n, uint32_t* column_id);
+
+/* Packs everything into the HBM container pool and precomputes the per-partition full-filter count
+ * tables (the K3 path of mutations.cpp:101-136). No ingest call is valid afterwards. */
+int sb_db_finalize(sb_db* db);
+
+/* ---- filter plans ------------------------------------------------------------------------------ */
+/* Postfix (children before parent) encoding of a compiled Operator tree; same 11 tags as
+ * operators::Type (include/silo/query_engine/operators/operator.h:10-22). */
+enum sb_op {
+   SB_EMPTY = 0, SB_FULL = 1, SB_INDEX_SCAN = 2, SB_INTERSECTION = 3, SB_COMPLEMENT = 4, SB_RANGE_SELECTION = 5,
+   SB_SELECTION = 6, SB_BITMAP_SELECTION = 7, SB_THRESHOLD = 8, SB_UNION = 9, SB_BITMAP_PRODUCER = 10
+};
+enum sb_comparator { SB_EQUALS = 0, SB_LESS = 1, SB_HIGHER = 2, SB_LESS_OR_EQUALS = 3, SB_HIGHER_OR_EQUALS = 4, SB_NOT_EQUALS = 5 };
+
+typedef struct sb_predicate {   /* CompareToValueSelection<T> (selection.cpp:134-193) */
+   uint32_t column_id;          /* from sb_column_add                                  */
+   int32_t comparator;          /* enum sb_comparator                                  */
+   int32_t i32;                 /* value for dtype 0                                   */
+   uint32_t u32;                /* value for dtype 2                                   */
+   double f64;                  /* value for dtype 1                                   */
+} sb_predicate;
+
+typedef struct sb_node {
+   int32_t op;                  /* enum sb_op                                                              */
+   uint32_t row_count;          /* every operator carries it (complement.cpp:52, full.cpp:26)              */
+   uint32_t n_children;         /* INTERSECTION / THRESHOLD: non-negated; UNION: all; COMPLEMENT: 1;
+                                   SELECTION: 0 or 1. Children precede the node: first the non-negated
+                                   ones in order, then the negated ones.                                   */
+   uint32_t n_negated;          /* INTERSECTION / THRESHOLD                                                */
+   uint32_t number_of_matchers; /* THRESHOLD (threshold.cpp:28-38: 0 < n < k)                              */
+   uint32_t match_exactly;      /* THRESHOLD                                                               */
+   /* INDEX_SCAN: either a registered bitmap (source 0, bitmap_id) or a stored position bitmap
+      (source 1: store_id, position, symbol)                                                               */
+   uint32_t source;
+   uint32_t bitmap_id;
+   uint32_t store_id;           /* also BITMAP_SELECTION: the store whose missing_symbol_bitmaps are probed */
+   uint32_t position;           /* also BITMAP_SELECTION: `value`                                          */
+   uint32_t symbol;
+   uint32_t contains;           /* BITMAP_SELECTION: 1 CONTAINS, 0 NOT_CONTAINS (bitmap_selection.h:14)     */
+   const uint32_t* ranges;      /* RANGE_SELECTION: n_ranges pairs [start, end)                            */
+   uint32_t n_ranges;
+   const sb_predicate* predicates; /* SELECTION                                                            */
+   uint32_t n_predicates;
+   const void* host_bitmap;     /* BITMAP_PRODUCER (and host-evaluated string Selections): portable bytes  */
+   size_t host_bitmap_len;
+} sb_node;
+
+/* ---- filter evaluation: replaces Operator::evaluate() (query_engine.cpp:48) -------------------- */
+/* Evaluates plan[i] (n_nodes[i] nodes) on partition partitions[i] for i < n; one batch = one query.
+ * results[i] receives an owned handle. */
+int sb_filter_eval_batch(sb_db* db, uint32_t n, const uint32_t* partitions, const sb_node* const* plans,
+                         const uint32_t* n_nodes, sb_result** results);
+int sb_filter_eval(sb_db* db, uint32_t partition, const sb_node* plan, uint32_t n_nodes, sb_result** result);
+int sb_result_cardinality(const sb_result* r, uint64_t* cardinality);
+/* Ascending row ids (what iterating the reference's OperatorResult yields). Call with out == NULL
+ * to get the count. Needed by the host-side actions that stay outside the hot path. */
+int sb_result_export_ids(const sb_result* r, uint32_t* out, size_t capacity, size_t* n);
+int sb_result_free(sb_result* r);
+
+/* ---- actions: replace Action::execute (query_engine.cpp:60) ------------------------------------ */
+/* Mutations<S>::calculateMutationsPerPosition (mutations.cpp:139-164) for the sequence `store_name`:
+ * counts[sym * length + pos], uint32 with wrap-around, summed over the n partitions given
+ * (results[i] belongs to partitions[i]). `counts` is a HOST buffer of n_symbols*length entries.
+ * Returns 0 and sets *produced = 0 (counts untouched) when every filter is empty, mirroring
+ * preFilterBitmaps (mutations.cpp:36-63) which then yields no entry for the sequence. */
+int sb_mutations(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
+                 sb_result* const* results, uint32_t* counts, size_t counts_len, int* produced);
+/* Same, but leaves the table in device memory (for an NCCL reduce over NVLink before the copy). */
+int sb_mutations_device(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
+                        sb_result* const* results, void* device_counts, size_t counts_len, int* produced);
+/* aggregateWithoutGrouping (aggregated.cpp:58-66): sum of cardinalities, uint32 wrap-around. */
+int sb_aggregated_count(sb_db* db, uint32_t n, sb_result* const* results, uint32_t* count);
+
+/* ---- introspection (mirrors /info?details=true, database.cpp:239-305) -------------------------- */
+typedef struct sb_pool_stats {
+   uint64_t array_containers, array_values, run_containers, run_values, run_count, bitset_containers, bitset_values;
+   uint64_t directory_bytes, payload_bytes, missing_bytes, full_table_bytes, total_device_bytes;
+   uint64_t n_stores, n_partitions, n_work_items, n_chunks;
+} sb_pool_stats;
+int sb_pool_get_stats(const sb_db* db, sb_pool_stats* out);
+/* Algorithmic bytes of sb_mutations for these results: payload+directory of every stored
+ * container of the partial partitions, their filters, missing bitmaps of filtered rows, the table. */
+int sb_mutations_algorithmic_bytes(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
+                                   sb_result* const* results, uint64_t* bytes);
+/* CUDA-event time of the kernels of the last sb_mutations* call on this db, in milliseconds
+ * (k1 = fused AND-popcount scan, total = first kernel to last kernel). */
+int sb_last_timing(const sb_db* db, float* k1_ms, float* total_ms, uint32_t* n_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SILO_B200_H */

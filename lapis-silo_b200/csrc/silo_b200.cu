@@ -1,0 +1,269 @@
+// libsilo_b200.so — C ABI (include/silo_b200.h) over the sm_100a kernels. One translation unit:
+// this file holds the database object and the ingest / finalize entry points, api_filter.inc the
+// filter evaluation (replaces Operator::evaluate), api_action.inc the Mutations / Aggregated actions.
+#include "common.cuh"
+#include "kernels_action.cuh"
+#include "kernels_filter.cuh"
+#include "pool.cuh"
+
+using namespace sb;
+
+namespace sb {
+
+struct PinnedBuffer {   // growable page-locked staging buffer
+   uint8_t* ptr = nullptr;
+   size_t capacity = 0;
+   ~PinnedBuffer() { if (ptr) cudaFreeHost(ptr); }
+   uint8_t* ensure(size_t n) {
+      if (n > capacity) {
+         if (ptr) cudaFreeHost(ptr);
+         capacity = std::max<size_t>(n * 2, 1 << 16);
+         SB_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ptr), capacity));
+      }
+      return ptr;
+   }
+};
+struct GrowDevice {
+   uint8_t* ptr = nullptr;
+   size_t capacity = 0;
+   ~GrowDevice() { if (ptr) cudaFree(ptr); }
+   uint8_t* ensure(size_t n) {
+      if (n > capacity) {
+         if (ptr) cudaFree(ptr);
+         capacity = std::max<size_t>(n * 2, 1 << 16);
+         SB_CUDA(cudaMalloc(reinterpret_cast<void**>(&ptr), capacity));
+      }
+      return ptr;
+   }
+};
+
+// device memory of one sb_filter_eval_batch call; shared by its results
+struct Slab {
+   int device;
+   cudaStream_t stream;
+   uint8_t* ptr = nullptr;
+   size_t bytes = 0;
+   ~Slab() { if (ptr) { cudaSetDevice(device); cudaFreeAsync(ptr, stream); } }
+};
+
+}  // namespace sb
+
+struct sb_result {
+   sb_db* db;
+   std::shared_ptr<Slab> slab;
+   uint32_t partition, n_words, n_words_padded;
+   const uint64_t* words;
+   const uint32_t* rank_local;
+   const uint32_t* rank_block;
+   uint64_t cardinality;
+};
+
+struct sb_db {
+   int device = 0;
+   uint32_t n_partitions = 0;
+   bool finalized = false;
+   std::mutex mutex;
+   cudaStream_t stream = nullptr;
+   cudaEvent_t ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr;
+   bool timing_valid = false, k1_ran = false;
+   uint32_t last_launches = 0;
+
+   std::vector<std::unique_ptr<HostStore>> stores;
+   std::vector<std::unique_ptr<Sequence>> seqs;
+   std::map<std::string, int> seq_by_name;
+   DeviceBuffer<SeqDev> d_seqs;
+
+   std::vector<RegContainer> reg_containers;
+   std::vector<uint16_t> reg_pool;
+   std::vector<RegisteredBitmap> reg_bitmaps;
+   DeviceBuffer<RegContainer> d_reg_containers;
+   DeviceBuffer<uint16_t> d_reg_pool;
+   std::vector<Column> columns;
+
+   PinnedBuffer staging, counts_host;
+   GrowDevice blob, scratch, action_scratch;
+   sb_pool_stats stats{};
+
+   ~sb_db() {
+      cudaSetDevice(device);
+      for (auto& c : columns) if (c.device) cudaFree(c.device);
+      if (ev_begin) { cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); }
+      if (stream) cudaStreamDestroy(stream);
+   }
+};
+
+namespace sb {
+inline void useDevice(const sb_db* db) { SB_CUDA(cudaSetDevice(db->device)); }
+}
+
+extern "C" {
+
+const char* sb_last_error(void) { return lastError().c_str(); }
+
+int sb_device_count(int* n) {
+   return guarded([&] { SB_CUDA(cudaGetDeviceCount(n)); });
+}
+
+int sb_db_create(int device, uint32_t n_partitions, sb_db** out) {
+   return guarded([&] {
+      int count = 0;
+      SB_CUDA(cudaGetDeviceCount(&count));
+      SB_REQUIRE(count > 0, "no CUDA device: libsilo_b200 has no CPU fallback");
+      SB_REQUIRE(device >= 0 && device < count, "invalid device index");
+      SB_REQUIRE(n_partitions > 0 && n_partitions < 65536, "n_partitions must be in [1, 65535]");
+      SB_CUDA(cudaSetDevice(device));
+      auto db = std::make_unique<sb_db>();
+      db->device = device;
+      db->n_partitions = n_partitions;
+      SB_CUDA(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
+      SB_CUDA(cudaEventCreate(&db->ev_begin));
+      SB_CUDA(cudaEventCreate(&db->ev_k1_begin));
+      SB_CUDA(cudaEventCreate(&db->ev_k1_end));
+      SB_CUDA(cudaEventCreate(&db->ev_end));
+      db->stats.n_partitions = n_partitions;
+      *out = db.release();
+   });
+}
+
+int sb_db_free(sb_db* db) {
+   return guarded([&] {
+      if (!db) return;
+      cudaSetDevice(db->device);
+      cudaStreamSynchronize(db->stream);
+      delete db;
+   });
+}
+
+int sb_bitmap_add_portable(sb_db* db, uint32_t partition, const void* bytes, size_t len, uint32_t* bitmap_id) {
+   return guarded([&] {
+      std::lock_guard<std::mutex> lock(db->mutex);
+      SB_REQUIRE(!db->finalized, "sb_bitmap_add_portable after sb_db_finalize");
+      SB_REQUIRE(partition < db->n_partitions, "partition out of range");
+      RegisteredBitmap bm{partition, uint32_t(db->reg_containers.size()), 0, 0};
+      parsePortable(static_cast<const uint8_t*>(bytes), len, [&](const ParsedContainer& c) {
+         while (db->reg_pool.size() % 8) db->reg_pool.push_back(0);
+         RegContainer rc{};
+         rc.pay_off = db->reg_pool.size();
+         rc.size = c.kind == KIND_BITSET ? c.card : c.size;
+         rc.key = c.key;
+         rc.kind = c.kind;
+         const uint32_t n16 = payloadU16(c);
+         db->reg_pool.insert(db->reg_pool.end(), c.data, c.data + n16);
+         db->reg_containers.push_back(rc);
+         bm.n_containers++;
+         uint32_t last = 0;
+         if (c.kind == KIND_ARRAY) last = c.data[c.size - 1];
+         else if (c.kind == KIND_RUN) last = uint32_t(c.data[2 * (c.size - 1)]) + c.data[2 * (c.size - 1) + 1];
+         else { const uint64_t* w = reinterpret_cast<const uint64_t*>(c.data); for (int k = 1023; k >= 0; --k) { uint64_t x; memcpy(&x, w + k, 8); if (x) { last = uint32_t(k) * 64 + 63 - __builtin_clzll(x); break; } } }
+         bm.max_value = (uint32_t(c.key) << 16) | last;
+      });
+      *bitmap_id = uint32_t(db->reg_bitmaps.size());
+      db->reg_bitmaps.push_back(bm);
+   });
+}
+
+int sb_store_add(sb_db* db, uint32_t partition, const char* name, int alphabet, uint32_t length, uint32_t n_rows,
+                 const uint8_t* blob, const uint64_t* slot_off, const int8_t* flipped, const int8_t* deleted,
+                 const uint8_t* missing_blob, const uint64_t* missing_off, uint32_t* store_id) {
+   return guarded([&] {
+      std::lock_guard<std::mutex> lock(db->mutex);
+      SB_REQUIRE(!db->finalized, "sb_store_add after sb_db_finalize");
+      SB_REQUIRE(partition < db->n_partitions, "partition out of range");
+      SB_REQUIRE(alphabet == 0 || alphabet == 1, "alphabet must be 0 (nucleotide) or 1 (amino acid)");
+      SB_REQUIRE(length > 0, "sequence length must be positive");
+      const uint32_t sigma = alphabet == 0 ? 16 : 25;
+      int seq_index;
+      auto it = db->seq_by_name.find(name);
+      if (it == db->seq_by_name.end()) {
+         auto seq = std::make_unique<Sequence>();
+         seq->name = name; seq->alphabet = alphabet; seq->length = length; seq->sigma = sigma;
+         seq->store_of_partition.assign(db->n_partitions, -1);
+         seq_index = int(db->seqs.size());
+         db->seq_by_name[name] = seq_index;
+         db->seqs.push_back(std::move(seq));
+      } else {
+         seq_index = it->second;
+         Sequence& seq = *db->seqs[seq_index];
+         SB_REQUIRE(seq.alphabet == alphabet && seq.length == length, std::string("store '") + name + "' registered with a different alphabet or length");
+      }
+      Sequence& seq = *db->seqs[seq_index];
+      SB_REQUIRE(seq.store_of_partition[partition] < 0, std::string("store '") + name + "' registered twice for one partition");
+      auto st = std::make_unique<HostStore>();
+      st->partition = partition; st->seq = uint32_t(seq_index); st->n_rows = n_rows;
+      st->flipped.assign(flipped, flipped + length);
+      st->deleted.assign(deleted, deleted + length);
+      for (uint32_t pos = 0; pos < length; ++pos) {
+         SB_REQUIRE(st->flipped[pos] >= -1 && st->flipped[pos] < int(sigma) && st->deleted[pos] >= -1 && st->deleted[pos] < int(sigma), "flipped / deleted symbol out of range");
+      }
+      const size_t n_slots = size_t(length) * sigma;
+      for (size_t slot = 0; slot < n_slots; ++slot) {
+         const uint64_t b = slot_off[slot], e = slot_off[slot + 1];
+         if (e == b) continue;
+         const uint32_t pos = uint32_t(slot / sigma), sym = uint32_t(slot - size_t(pos) * sigma);
+         // the reference never reads the bitmap of the deleted symbol (mutations.cpp:74-83)
+         const bool is_deleted = st->deleted[pos] == int(sym);
+         parsePortable(blob + b, e - b, [&](const ParsedContainer& c) {
+            if (is_deleted) return;
+            TmpContainer t{uint32_t(slot), c.key, c.kind, c.kind == KIND_BITSET ? c.card : c.size, st->payload.size()};
+            const uint32_t n16 = payloadU16(c);
+            st->payload.insert(st->payload.end(), c.data, c.data + n16);
+            st->containers.push_back(t);
+            st->alg_bytes += (c.kind == KIND_BITSET ? 8192 : c.kind == KIND_ARRAY ? 2 * c.size : 4 * c.size) + 8;
+            st->dir_bytes += 8;
+         });
+      }
+      st->miss_row_off.resize(size_t(n_rows) + 1, 0);
+      st->miss_row_bytes.resize(n_rows, 0);
+      for (uint32_t row = 0; row < n_rows; ++row) {
+         st->miss_row_off[row] = uint32_t(st->miss_iv.size());
+         const uint64_t b = missing_off[row], e = missing_off[row + 1];
+         uint32_t bytes = 0;
+         parsePortable(missing_blob + b, e - b, [&](const ParsedContainer& c) {
+            const uint32_t base = uint32_t(c.key) << 16;
+            auto push = [&](uint32_t start, uint32_t end) {   // [start, end), merged with an adjacent predecessor
+               if (st->miss_iv.size() > st->miss_row_off[row] && st->miss_iv.back().y == start) st->miss_iv.back().y = end;
+               else st->miss_iv.push_back(make_uint2(start, end));
+            };
+            if (c.kind == KIND_RUN) {
+               for (uint32_t r = 0; r < c.size; ++r) push(base + c.data[2 * r], base + c.data[2 * r] + c.data[2 * r + 1] + 1);
+               bytes += 4 * c.size;
+            } else if (c.kind == KIND_ARRAY) {
+               for (uint32_t k = 0; k < c.size; ++k) push(base + c.data[k], base + c.data[k] + 1);
+               bytes += 2 * c.size;
+            } else {
+               const uint64_t* w = reinterpret_cast<const uint64_t*>(c.data);
+               for (uint32_t k = 0; k < 1024; ++k) { uint64_t x; memcpy(&x, w + k, 8); while (x) { const uint32_t bit = __builtin_ctzll(x); push(base + k * 64 + bit, base + k * 64 + bit + 1); x &= x - 1; } }
+               bytes += 8192;
+            }
+         });
+         st->miss_row_bytes[row] = bytes;
+         st->miss_alg_bytes += bytes + 4;
+      }
+      st->miss_row_off[n_rows] = uint32_t(st->miss_iv.size());
+      seq.store_of_partition[partition] = int(db->stores.size());
+      *store_id = uint32_t(db->stores.size());
+      db->stores.push_back(std::move(st));
+      db->stats.n_stores++;
+   });
+}
+
+int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, uint32_t n, uint32_t* column_id) {
+   return guarded([&] {
+      std::lock_guard<std::mutex> lock(db->mutex);
+      SB_REQUIRE(partition < db->n_partitions, "partition out of range");
+      SB_REQUIRE(dtype >= 0 && dtype <= 2, "dtype must be 0 (int32), 1 (float64) or 2 (uint32 date)");
+      useDevice(db);
+      Column c{partition, dtype, n, nullptr};
+      const size_t bytes = size_t(n) * (dtype == 1 ? 8 : 4);
+      SB_CUDA(cudaMalloc(&c.device, std::max<size_t>(bytes, 16)));
+      if (bytes) SB_CUDA(cudaMemcpy(c.device, values, bytes, cudaMemcpyHostToDevice));
+      *column_id = uint32_t(db->columns.size());
+      db->columns.push_back(c);
+      db->stats.total_device_bytes += bytes;
+   });
+}
+
+}  // extern "C"
+
+#include "api_filter.inc"
+#include "api_action.inc"

@@ -1,0 +1,160 @@
+// C entry points of the GPU query engine for ctypes (tests, bench.py, __graft_entry__) — the same calls
+// a C++ host makes through engine.hpp. Every bitmap operation runs in libsilo_b200.so.
+#include "capi_common.hpp"
+#include "engine.hpp"
+
+using namespace silo;
+using engine::DeviceDatabase;
+
+namespace {
+
+int exportIds(const DeviceDatabase::EvaluatedFilters& filters, size_t index, uint32_t** ids, size_t* n) {
+   size_t count = 0;
+   engine::check(sb_result_export_ids(filters.results.at(index), nullptr, 0, &count));
+   *ids = static_cast<uint32_t*>(malloc(std::max<size_t>(1, count) * sizeof(uint32_t)));
+   engine::check(sb_result_export_ids(filters.results.at(index), *ids, count, n));
+   return 0;
+}
+
+// One query in flight across ranks: local filters evaluated, tables reduced by the caller (NCCL), then finished.
+struct QueryState {
+   const DeviceDatabase* device_db;
+   Query query;
+   DeviceDatabase::EvaluatedFilters filters;
+   std::vector<std::string> names;
+   std::map<std::string, std::vector<uint32_t>> tables;   // reduced tables handed back by the caller
+};
+
+}  // namespace
+
+extern "C" {
+
+// `partitions` = global partition indices this GPU owns (all when n == 0)
+void* silo_engine_create(const void* db_, int device, const uint32_t* partitions, uint32_t n) {
+   DeviceDatabase* out = nullptr;
+   capi::guarded([&] {
+      const auto& db = *static_cast<const Database*>(db_);
+      std::vector<uint32_t> owned(partitions, partitions + n);
+      if (n == 0) for (uint32_t p = 0; p < db.partitions.size(); ++p) owned.push_back(p);
+      out = new DeviceDatabase(db, device, std::move(owned));
+   });
+   return out;
+}
+void silo_engine_free(void* engine) { delete static_cast<DeviceDatabase*>(engine); }
+void* silo_engine_handle(void* engine) { return static_cast<DeviceDatabase*>(engine)->handle; }
+
+// QueryEngine::executeQuery (query_engine.cpp:30-68) -> {"queryResult": [...]}
+char* silo_engine_execute(void* engine, const char* query_json) {
+   char* out = nullptr;
+   capi::guarded([&] { out = capi::dupString(toJson(static_cast<DeviceDatabase*>(engine)->executeQuery(query_json)).dump()); });
+   return out;
+}
+
+// Full uint32[sigma][L] table of one sequence; returns 4 (table zeroed) when no partition passes the filter.
+int silo_engine_mutation_counts(void* engine_, const char* query_json, const char* sequence_name, uint32_t* out, size_t out_len) {
+   int status = 0;
+   const int rc = capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      Query query = parseQuery(query_json);
+      auto filters = engine.evaluateFilter(*query.filter);
+      std::vector<uint32_t> counts;
+      const bool produced = engine.mutationCounts(filters, sequence_name, query.action.alphabetId(), counts);
+      if (counts.size() != out_len) throw std::runtime_error("count table size mismatch");
+      memcpy(out, counts.data(), out_len * sizeof(uint32_t));
+      if (!produced) status = 4;
+   });
+   return rc ? rc : status;
+}
+
+int silo_engine_filter_ids(void* engine_, const char* filter_json, uint32_t local_partition, uint32_t** ids, size_t* n) {
+   return capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      auto expression = filter::parseExpression(json::parse(filter_json));
+      auto op = expression->compile(engine.db, *engine.db.partitions.at(engine.owned.at(local_partition)), filter::AmbiguityMode::NONE);
+      DeviceDatabase::Plan plan;
+      engine.lower(*op, local_partition, plan);
+      DeviceDatabase::EvaluatedFilters filters;
+      filters.handle = engine.handle;
+      filters.partitions = {local_partition};
+      filters.results = {nullptr};
+      engine::check(sb_filter_eval(engine.handle, local_partition, plan.nodes.data(), static_cast<uint32_t>(plan.nodes.size()), &filters.results[0]));
+      exportIds(filters, 0, ids, n);
+   });
+}
+
+// Operator known-answer tests: a literal operator tree evaluated on the GPU.
+int silo_engine_eval_optree(int device, const char* optree_json, uint32_t** ids, size_t* n) {
+   return capi::guarded([&] {
+      static const Database empty_database;
+      auto holder = opTreeFromJson(optree_json);
+      DeviceDatabase engine(empty_database, device, *holder);
+      auto filters = engine.evaluateTrees({holder->root.get()});
+      exportIds(filters, 0, ids, n);
+   });
+}
+
+// ---- multi-GPU protocol: begin (local filters) -> per-sequence device tables -> caller reduces -> finish ----
+void* silo_query_begin(void* engine_, const char* query_json) {
+   QueryState* state = nullptr;
+   capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      auto s = std::make_unique<QueryState>();
+      s->device_db = &engine;
+      s->query = parseQuery(query_json);
+      s->query.action.validateOrderByFields();
+      if (s->query.action.type != ActionType::AGGREGATED) s->names = engine.mutationSequenceNames(s->query.action);
+      else if (!s->query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+      s->filters = engine.evaluateFilter(*s->query.filter);
+      state = s.release();
+   });
+   return state;
+}
+void silo_query_free(void* state) { delete static_cast<QueryState*>(state); }
+uint32_t silo_query_sequence_count(void* state) { return static_cast<uint32_t>(static_cast<QueryState*>(state)->names.size()); }
+const char* silo_query_sequence_name(void* state, uint32_t i) { return static_cast<QueryState*>(state)->names.at(i).c_str(); }
+uint64_t silo_query_table_len(void* state_, uint32_t i) {
+   auto* s = static_cast<QueryState*>(state_);
+   const int alphabet_id = s->query.action.alphabetId();
+   return uint64_t(alphabetById(alphabet_id).count) * s->device_db->db.getReferences(alphabet_id).at(s->names.at(i)).size();
+}
+int silo_query_local_count(void* state_, uint32_t* count) {
+   return capi::guarded([&] { auto* s = static_cast<QueryState*>(state_); *count = s->device_db->aggregatedCount(s->filters); });
+}
+// local table of sequence i into DEVICE memory (a torch tensor's data_ptr); produced = 0 if all local filters are empty
+int silo_query_local_table_device(void* state_, uint32_t i, void* device_counts, uint64_t len, int* produced) {
+   return capi::guarded([&] {
+      auto* s = static_cast<QueryState*>(state_);
+      engine::check(sb_mutations_device(s->device_db->handle, s->names.at(i).c_str(), static_cast<uint32_t>(s->filters.results.size()),
+                                        s->filters.partitions.data(), s->filters.results.data(), device_counts, len, produced));
+   });
+}
+int silo_query_set_table(void* state_, uint32_t i, const uint32_t* counts, uint64_t len) {
+   return capi::guarded([&] { auto* s = static_cast<QueryState*>(state_); s->tables[s->names.at(i)].assign(counts, counts + len); });
+}
+// root rank: assemble the result from the reduced tables / the reduced count
+char* silo_query_finish(void* state_, uint32_t reduced_count) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      auto* s = static_cast<QueryState*>(state_);
+      const Action& action = s->query.action;
+      QueryResult result = action.executeAndOrder([&]() -> QueryResult {
+         if (action.type == ActionType::AGGREGATED) {
+            QueryResultEntry entry;
+            entry.fields["count"] = static_cast<int32_t>(reduced_count);
+            return QueryResult{{entry}};
+         }
+         QueryResult r;
+         const int alphabet_id = action.alphabetId();
+         for (const auto& name : s->names) {
+            auto it = s->tables.find(name);
+            if (it == s->tables.end()) continue;
+            addMutationsToOutput(name, alphabetById(alphabet_id), s->device_db->db.getReferences(alphabet_id).at(name), it->second.data(), action.min_proportion, r.query_result);
+         }
+         return r;
+      });
+      out = capi::dupString(toJson(result).dump());
+   });
+   return out;
+}
+
+}  // extern "C"

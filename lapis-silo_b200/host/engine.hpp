@@ -1,0 +1,342 @@
+// Host side of the GPU query path: mirrors QueryEngine::executeQuery
+// (src/silo/query_engine/query_engine.cpp:30-68). Everything that touches a bitmap goes through the
+// C ABI of libsilo_b200.so (include/silo_b200.h); this file only
+//   * ingests a silo::Database into an sb_db (what a loader would do after
+//     Database::loadDatabaseState, src/silo/database.cpp:480-560),
+//   * lowers a compiled Operator tree to the postfix sb_node plan,
+//   * runs M5/M6 of the Mutations action (thresholds, double division, rows) and Aggregated's row.
+// There is no CPU evaluation of operators here: sb_* failures surface as exceptions.
+#pragma once
+#include <deque>
+#include <unordered_map>
+
+#include "../../include/silo_b200.h"
+#include "optree_json.hpp"
+#include "query.hpp"
+
+namespace silo::engine {
+
+struct DeviceError : std::runtime_error { using std::runtime_error::runtime_error; };
+inline void check(int rc) { if (rc != 0) throw DeviceError(std::string("silo_b200: ") + sb_last_error()); }
+
+// Concatenated CRoaring portable serializations (what roaring_serialize.h:23-28 writes per bitmap)
+struct PortableBlob {
+   std::string bytes;
+   std::vector<uint64_t> offsets{0};
+   void add(const Bitmap& bm) {
+      if (!bm.isEmpty()) bm.writePortable(bytes);
+      offsets.push_back(bytes.size());
+   }
+};
+
+class DeviceDatabase {
+  public:
+   const Database& db;
+   std::vector<uint32_t> owned;   // global partition index of each device-local partition
+   sb_db* handle = nullptr;
+
+   DeviceDatabase(const Database& database, int device, std::vector<uint32_t> owned_partitions) : db(database), owned(std::move(owned_partitions)) {
+      check(sb_db_create(device, static_cast<uint32_t>(owned.size()), &handle));
+      try {
+         for (uint32_t local = 0; local < owned.size(); ++local) ingestPartition(local, *db.partitions.at(owned[local]));
+         std::sort(store_ranges.begin(), store_ranges.end(), [](const StoreRange& a, const StoreRange& b) { return a.begin < b.begin; });
+         check(sb_db_finalize(handle));
+      } catch (...) { sb_db_free(handle); handle = nullptr; throw; }
+   }
+   // Stand-alone operator trees (the reference's operator unit tests): one partition holding the
+   // tree's literal missing-symbol stores and columns; literal index bitmaps travel with the plan.
+   DeviceDatabase(const Database& empty_database, int device, const OpTreeHolder& holder) : db(empty_database), owned{0} {
+      check(sb_db_create(device, 1, &handle));
+      try {
+         uint32_t counter = 0;
+         for (const auto& store : holder.stores) {
+            uint32_t length = 1;
+            for (const auto& bm : store.missing_symbol_bitmaps) if (!bm.isEmpty()) length = std::max(length, bm.maximum() + 1);
+            PortableBlob missing;
+            for (const auto& bm : store.missing_symbol_bitmaps) missing.add(bm);
+            const std::vector<uint64_t> slot_off(size_t(length) * 16 + 1, 0);
+            const std::vector<int8_t> none(length, -1);
+            const uint8_t dummy = 0;
+            uint32_t store_id = 0;
+            check(sb_store_add(handle, 0, ("kat" + std::to_string(counter++)).c_str(), 0, length, static_cast<uint32_t>(store.missing_symbol_bitmaps.size()),
+                               &dummy, slot_off.data(), none.data(), none.data(), reinterpret_cast<const uint8_t*>(missing.bytes.data()), missing.offsets.data(), &store_id));
+            store_ids[&store] = store_id;
+         }
+         auto addColumn = [&](int dtype, const void* data, size_t n) {
+            if (n == 0) return;
+            uint32_t id = 0;
+            check(sb_column_add(handle, 0, dtype, data, static_cast<uint32_t>(n), &id));
+            column_ids[data] = id;
+         };
+         for (const auto& c : holder.int_columns) addColumn(0, c.data(), c.size());
+         for (const auto& c : holder.float_columns) addColumn(1, c.data(), c.size());
+         for (const auto& c : holder.date_columns) addColumn(2, c.data(), c.size());
+         check(sb_db_finalize(handle));
+      } catch (...) { sb_db_free(handle); handle = nullptr; throw; }
+   }
+   DeviceDatabase(const DeviceDatabase&) = delete;
+   ~DeviceDatabase() { if (handle) sb_db_free(handle); }
+
+   // ---- plan lowering -------------------------------------------------------------------------------
+   struct Plan {
+      std::vector<sb_node> nodes;
+      std::deque<std::vector<uint32_t>> ranges;
+      std::deque<std::vector<sb_predicate>> predicates;
+      std::deque<std::string> host_bitmaps;
+   };
+
+   void lower(const operators::Operator& op, uint32_t local_partition, Plan& plan) const {
+      using namespace operators;
+      sb_node node{};
+      node.row_count = op.row_count;
+      switch (op.type()) {
+         case EMPTY: node.op = SB_EMPTY; break;
+         case FULL: node.op = SB_FULL; break;
+         case INDEX_SCAN: {
+            node.op = SB_INDEX_SCAN;
+            if (const StoreRange* range = findStore(op.bitmap)) {
+               const size_t slot = static_cast<size_t>(op.bitmap - range->begin);
+               node.source = 1; node.store_id = range->store_id;
+               node.position = static_cast<uint32_t>(slot / range->sigma); node.symbol = static_cast<uint32_t>(slot % range->sigma);
+            } else if (auto it = bitmap_ids.find(op.bitmap); it != bitmap_ids.end()) {
+               node.source = 0; node.bitmap_id = it->second;
+            } else {   // a bitmap the pool does not hold (operator unit tests): ship it like a producer result
+               pushHostBitmap(node, *op.bitmap, plan);
+            }
+            break;
+         }
+         case BITMAP_PRODUCER: pushHostBitmap(node, op.producer(), plan); break;
+         case BITMAP_SELECTION: {
+            node.op = SB_BITMAP_SELECTION;
+            auto it = store_ids.find(op.store);
+            if (it == store_ids.end()) throw DeviceError("BitmapSelection over a store that is not in the device pool");
+            node.store_id = it->second; node.position = op.value; node.contains = op.contains ? 1 : 0;
+            break;
+         }
+         case RANGE_SELECTION: {
+            node.op = SB_RANGE_SELECTION;
+            plan.ranges.emplace_back();
+            for (const auto& r : op.ranges) { plan.ranges.back().push_back(r.start); plan.ranges.back().push_back(r.end); }
+            node.ranges = plan.ranges.back().data(); node.n_ranges = static_cast<uint32_t>(op.ranges.size());
+            break;
+         }
+         case COMPLEMENT: lower(*op.children[0], local_partition, plan); node.op = SB_COMPLEMENT; node.n_children = 1; break;
+         case UNION:
+            for (const auto& c : op.children) lower(*c, local_partition, plan);
+            node.op = SB_UNION; node.n_children = static_cast<uint32_t>(op.children.size());
+            break;
+         case INTERSECTION:
+         case THRESHOLD:
+            for (const auto& c : op.children) lower(*c, local_partition, plan);
+            for (const auto& c : op.negated_children) lower(*c, local_partition, plan);
+            node.op = op.type() == INTERSECTION ? SB_INTERSECTION : SB_THRESHOLD;
+            node.n_children = static_cast<uint32_t>(op.children.size()); node.n_negated = static_cast<uint32_t>(op.negated_children.size());
+            node.number_of_matchers = op.number_of_matchers; node.match_exactly = op.match_exactly ? 1 : 0;
+            break;
+         case SELECTION: lowerSelection(op, local_partition, plan); return;
+      }
+      plan.nodes.push_back(node);
+   }
+
+   // ---- query execution (query_engine.cpp:30-68) ------------------------------------------------------
+   struct EvaluatedFilters {
+      sb_db* handle = nullptr;
+      std::vector<uint32_t> partitions;
+      std::vector<sb_result*> results;
+      EvaluatedFilters() = default;
+      EvaluatedFilters(const EvaluatedFilters&) = delete;
+      EvaluatedFilters(EvaluatedFilters&& o) noexcept : handle(o.handle), partitions(std::move(o.partitions)), results(std::move(o.results)) { o.results.clear(); }
+      EvaluatedFilters& operator=(EvaluatedFilters&& o) noexcept {
+         if (this != &o) { for (auto* r : results) if (r) sb_result_free(r); handle = o.handle; partitions = std::move(o.partitions); results = std::move(o.results); o.results.clear(); }
+         return *this;
+      }
+      ~EvaluatedFilters() { for (auto* r : results) if (r) sb_result_free(r); }
+   };
+
+   EvaluatedFilters evaluateTrees(const std::vector<const operators::Operator*>& trees) const {
+      std::vector<Plan> plans(trees.size());
+      std::vector<const sb_node*> plan_ptrs;
+      std::vector<uint32_t> plan_sizes;
+      EvaluatedFilters out;
+      out.handle = handle;
+      for (uint32_t local = 0; local < trees.size(); ++local) {
+         lower(*trees[local], local, plans[local]);
+         plan_ptrs.push_back(plans[local].nodes.data());
+         plan_sizes.push_back(static_cast<uint32_t>(plans[local].nodes.size()));
+         out.partitions.push_back(local);
+      }
+      out.results.assign(trees.size(), nullptr);
+      if (!trees.empty()) check(sb_filter_eval_batch(handle, static_cast<uint32_t>(trees.size()), out.partitions.data(), plan_ptrs.data(), plan_sizes.data(), out.results.data()));
+      return out;
+   }
+
+   EvaluatedFilters evaluateFilter(const filter::Expression& expression) const {
+      std::vector<operators::OperatorPtr> trees;
+      std::vector<const operators::Operator*> ptrs;
+      for (uint32_t global : owned) {   // compile per partition (query_engine.cpp:41-46); evaluation is one batched call
+         trees.push_back(expression.compile(db, *db.partitions[global], filter::AmbiguityMode::NONE));
+         ptrs.push_back(trees.back().get());
+      }
+      return evaluateTrees(ptrs);
+   }
+
+   std::vector<std::string> mutationSequenceNames(const Action& action) const {   // mutations.cpp:240-252
+      const Alphabet& alphabet = alphabetById(action.alphabetId());
+      const auto& references = db.getReferences(action.alphabetId());
+      std::vector<std::string> names;
+      for (const auto& name : action.sequence_names) {
+         CHECK_SILO_QUERY(references.count(name), "Database does not contain the " + std::string(alphabet.name_lower) + " sequence with name: '" + name + "'")
+         names.push_back(name);
+      }
+      if (action.sequence_names.empty()) for (const auto& [name, _] : references) names.push_back(name);
+      return names;
+   }
+
+   // counts table of one sequence; false when every local filter is empty (no table, mutations.cpp:36-63)
+   bool mutationCounts(const EvaluatedFilters& filters, const std::string& name, int alphabet_id, std::vector<uint32_t>& counts) const {
+      const auto& reference = db.getReferences(alphabet_id).at(name);
+      counts.assign(size_t(alphabetById(alphabet_id).count) * reference.size(), 0);
+      int produced = 0;
+      check(sb_mutations(handle, name.c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(), filters.results.data(), counts.data(), counts.size(), &produced));
+      return produced != 0;
+   }
+
+   uint32_t aggregatedCount(const EvaluatedFilters& filters) const {
+      uint32_t count = 0;
+      check(sb_aggregated_count(handle, static_cast<uint32_t>(filters.results.size()), filters.results.data(), &count));
+      return count;
+   }
+
+   QueryResult executeQuery(const std::string& query_string, std::map<std::string, std::vector<uint32_t>>* tables = nullptr) const {
+      Query query = parseQuery(query_string);
+      EvaluatedFilters filters = evaluateFilter(*query.filter);
+      return query.action.executeAndOrder([&]() -> QueryResult {
+         if (query.action.type == ActionType::AGGREGATED) {
+            if (!query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+            QueryResultEntry entry;
+            entry.fields["count"] = static_cast<int32_t>(aggregatedCount(filters));   // aggregated.cpp:58-66
+            return QueryResult{{entry}};
+         }
+         const int alphabet_id = query.action.alphabetId();
+         QueryResult result;
+         std::vector<uint32_t> counts;
+         for (const auto& name : mutationSequenceNames(query.action)) {   // mutations.cpp:258-270
+            if (!mutationCounts(filters, name, alphabet_id, counts)) continue;
+            addMutationsToOutput(name, alphabetById(alphabet_id), db.getReferences(alphabet_id).at(name), counts.data(), query.action.min_proportion, result.query_result);
+            if (tables) (*tables)[name] = counts;
+         }
+         return result;
+      });
+   }
+
+  private:
+   struct StoreRange { const Bitmap* begin; const Bitmap* end; uint32_t store_id; uint32_t sigma; };
+   std::vector<StoreRange> store_ranges;
+   std::unordered_map<const SequenceStorePartition*, uint32_t> store_ids;
+   std::unordered_map<const Bitmap*, uint32_t> bitmap_ids;
+   std::unordered_map<const void*, uint32_t> column_ids;
+
+   const StoreRange* findStore(const Bitmap* bm) const {
+      auto it = std::upper_bound(store_ranges.begin(), store_ranges.end(), bm, [](const Bitmap* b, const StoreRange& r) { return b < r.begin; });
+      if (it == store_ranges.begin()) return nullptr;
+      --it;
+      return bm < it->end ? &*it : nullptr;
+   }
+
+   static void pushHostBitmap(sb_node& node, const Bitmap& bm, Plan& plan) {
+      node.op = SB_BITMAP_PRODUCER;
+      plan.host_bitmaps.emplace_back(bm.isEmpty() ? std::string() : bm.toPortable());
+      node.host_bitmap = plan.host_bitmaps.back().data();
+      node.host_bitmap_len = plan.host_bitmaps.back().size();
+   }
+
+   // Selection (selection.cpp:92-109): numeric / date predicates run on the GPU; SiloString predicates
+   // are evaluated on the host and shipped as a bitmap; the parts are intersected.
+   void lowerSelection(const operators::Operator& op, uint32_t local_partition, Plan& plan) const {
+      using namespace operators;
+      uint32_t parts = 0;
+      if (!op.children.empty()) { lower(*op.children[0], local_partition, plan); ++parts; }
+      std::vector<sb_predicate> device_preds;
+      std::vector<const Predicate*> host_preds;
+      for (const auto& p : op.predicates) {
+         if (p.kind == ColumnKind::STRING) { host_preds.push_back(&p); continue; }
+         sb_predicate d{};
+         const void* key = p.kind == ColumnKind::INT32 ? static_cast<const void*>(static_cast<const std::vector<int32_t>*>(p.column)->data())
+                         : p.kind == ColumnKind::FLOAT64 ? static_cast<const void*>(static_cast<const std::vector<double>*>(p.column)->data())
+                                                         : static_cast<const void*>(static_cast<const std::vector<uint32_t>*>(p.column)->data());
+         auto it = column_ids.find(key);
+         if (it == column_ids.end() && op.row_count == 0) continue;   // empty partition: nothing to compare
+         if (it == column_ids.end()) throw DeviceError("Selection over a column that is not in the device pool");
+         d.column_id = it->second;
+         d.comparator = static_cast<int32_t>(p.comparator);
+         d.i32 = p.int_value; d.u32 = p.date_value; d.f64 = p.float_value;
+         device_preds.push_back(d);
+      }
+      if (!device_preds.empty() || (host_preds.empty() && op.children.empty())) {
+         sb_node node{};
+         node.op = SB_SELECTION; node.row_count = op.row_count;
+         plan.predicates.push_back(std::move(device_preds));
+         node.predicates = plan.predicates.back().data(); node.n_predicates = static_cast<uint32_t>(plan.predicates.back().size());
+         plan.nodes.push_back(node);
+         ++parts;
+      }
+      if (!host_preds.empty()) {
+         std::vector<uint32_t> rows;
+         for (uint32_t row = 0; row < op.row_count; ++row) {
+            bool ok = true;
+            for (const auto* p : host_preds) if (!p->match(row)) { ok = false; break; }
+            if (ok) rows.push_back(row);
+         }
+         sb_node node{};
+         node.row_count = op.row_count;
+         pushHostBitmap(node, Bitmap::fromSorted(rows.data(), rows.size()), plan);
+         plan.nodes.push_back(node);
+         ++parts;
+      }
+      if (parts > 1) {
+         sb_node node{};
+         node.op = SB_INTERSECTION; node.row_count = op.row_count; node.n_children = parts;
+         plan.nodes.push_back(node);
+      }
+   }
+
+   void ingestStore(uint32_t local, const std::string& name, const SequenceStorePartition& store) {
+      PortableBlob blob, missing;
+      blob.offsets.reserve(store.bitmaps.size() + 1);
+      for (const auto& bm : store.bitmaps) blob.add(bm);
+      missing.offsets.reserve(store.missing_symbol_bitmaps.size() + 1);
+      for (const auto& bm : store.missing_symbol_bitmaps) missing.add(bm);
+      uint32_t store_id = 0;
+      check(sb_store_add(handle, local, name.c_str(), store.alphabet->id, store.length(), static_cast<uint32_t>(store.missing_symbol_bitmaps.size()),
+                         reinterpret_cast<const uint8_t*>(blob.bytes.data()), blob.offsets.data(), store.flipped.data(), store.deleted.data(),
+                         reinterpret_cast<const uint8_t*>(missing.bytes.data()), missing.offsets.data(), &store_id));
+      store_ids[&store] = store_id;
+      if (!store.bitmaps.empty()) store_ranges.push_back({store.bitmaps.data(), store.bitmaps.data() + store.bitmaps.size(), store_id, store.alphabet->count});
+   }
+
+   void ingestIndex(uint32_t local, const std::unordered_map<uint32_t, Bitmap>& index) {
+      for (const auto& [id, bm] : index) {
+         const std::string bytes = bm.isEmpty() ? std::string() : bm.toPortable();
+         uint32_t bitmap_id = 0;
+         check(sb_bitmap_add_portable(handle, local, bytes.data(), bytes.size(), &bitmap_id));
+         bitmap_ids[&bm] = bitmap_id;
+      }
+   }
+
+   void ingestPartition(uint32_t local, const DatabasePartition& part) {
+      for (const auto& [name, store] : part.nuc_sequences) ingestStore(local, name, store);
+      for (const auto& [name, store] : part.aa_sequences) ingestStore(local, name, store);
+      for (const auto& [name, col] : part.columns.pango_lineage_columns) { ingestIndex(local, col.indexed_values); ingestIndex(local, col.indexed_sublineage_values); }
+      for (const auto& [name, col] : part.columns.indexed_string_columns) ingestIndex(local, col.indexed_values);
+      auto addColumn = [&](int dtype, const void* data, size_t n) {
+         uint32_t id = 0;
+         check(sb_column_add(handle, local, dtype, data, static_cast<uint32_t>(n), &id));
+         column_ids[data] = id;
+      };
+      for (const auto& [name, col] : part.columns.int_columns) if (!col.values.empty()) addColumn(0, col.values.data(), col.values.size());
+      for (const auto& [name, col] : part.columns.float_columns) if (!col.values.empty()) addColumn(1, col.values.data(), col.values.size());
+      for (const auto& [name, col] : part.columns.date_columns) if (!col.values.empty()) addColumn(2, col.values.data(), col.values.size());
+   }
+};
+
+}  // namespace silo::engine

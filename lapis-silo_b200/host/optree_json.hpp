@@ -39,7 +39,9 @@ inline operators::Comparator parseComparator(const std::string& s) {
    throw std::runtime_error("bad comparator " + s);
 }
 
-inline operators::OperatorPtr buildOpTree(const json::Value& j, uint32_t inherited_row_count, OpTreeHolder& holder) {
+inline operators::OperatorPtr buildOpTree(const json::Value& j, uint32_t inherited_row_count, OpTreeHolder& holder);
+
+inline operators::OperatorPtr buildOpTreeNode(const json::Value& j, uint32_t inherited_row_count, OpTreeHolder& holder) {
    using namespace operators;
    const uint32_t rc = j.contains("row_count") ? static_cast<uint32_t>(j["row_count"].as_int()) : inherited_row_count;
    const std::string op = j["op"].as_string();
@@ -106,6 +108,13 @@ inline operators::OperatorPtr buildOpTree(const json::Value& j, uint32_t inherit
       return makeSelection(std::move(child), std::move(predicates), rc);
    }
    throw std::runtime_error("unknown op '" + op + "'");
+}
+
+// "negate": true applies Operator::negate() to the node (the reference tests call under_test.negate())
+inline operators::OperatorPtr buildOpTree(const json::Value& j, uint32_t inherited_row_count, OpTreeHolder& holder) {
+   auto op = buildOpTreeNode(j, inherited_row_count, holder);
+   if (j.contains("negate") && j["negate"].b) return op->negate();
+   return op;
 }
 
 }  // namespace detail

@@ -1,0 +1,214 @@
+"""ctypes bindings of the product libraries (libsilo_host.so -> libsilo_b200.so).
+
+Python is only the harness here (tests, bench.py, smoke): the host logic is C++ (host/*.hpp) and the
+bitmap work is CUDA (csrc/). Nothing in this module computes a query result; a missing library or a
+missing GPU raises.
+"""
+import ctypes
+import json
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+PKG = Path(__file__).resolve().parent
+ROOT = PKG.parent
+SIGMA = {0: 16, 1: 25}
+
+_host = None
+
+
+def build(force=False):
+    """Compile libsilo_b200.so (nvcc, sm_100a) and libsilo_host.so (g++) in-tree."""
+    args = ["make", "-C", str(PKG)] + (["-B"] if force else []) + ["all"]
+    subprocess.run(args, check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+
+
+def host():
+    global _host
+    if _host is not None:
+        return _host
+    for name in ("libsilo_b200.so", "libsilo_host.so"):
+        if not (PKG / name).exists():
+            raise RuntimeError(f"{name} is not built: run `make -C {PKG}` (there is no fallback path)")
+    ctypes.CDLL(str(PKG / "libsilo_b200.so"), mode=ctypes.RTLD_GLOBAL)
+    lib = ctypes.CDLL(str(PKG / "libsilo_host.so"), mode=ctypes.RTLD_GLOBAL)
+    vp, cp, u32, u64, sz = ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_size_t
+    pu32 = ctypes.POINTER(ctypes.c_uint32)
+    sig = {
+        "silo_last_error": (cp, []),
+        "silo_free": (None, [vp]),
+        "silo_db_build_from_dir": (vp, [cp]),
+        "silo_db_free": (None, [vp]),
+        "silo_db_partition_count": (u32, [vp]),
+        "silo_db_partition_rows": (u32, [vp, u32]),
+        "silo_db_info_json": (vp, [vp]),
+        "silo_engine_create": (vp, [vp, ctypes.c_int, pu32, u32]),
+        "silo_engine_free": (None, [vp]),
+        "silo_engine_handle": (vp, [vp]),
+        "silo_engine_execute": (vp, [vp, cp]),
+        "silo_engine_mutation_counts": (ctypes.c_int, [vp, cp, cp, vp, sz]),
+        "silo_engine_filter_ids": (ctypes.c_int, [vp, cp, u32, ctypes.POINTER(vp), ctypes.POINTER(sz)]),
+        "silo_engine_eval_optree": (ctypes.c_int, [ctypes.c_int, cp, ctypes.POINTER(vp), ctypes.POINTER(sz)]),
+        "silo_query_begin": (vp, [vp, cp]),
+        "silo_query_free": (None, [vp]),
+        "silo_query_sequence_count": (u32, [vp]),
+        "silo_query_sequence_name": (cp, [vp, u32]),
+        "silo_query_table_len": (u64, [vp, u32]),
+        "silo_query_local_count": (ctypes.c_int, [vp, pu32]),
+        "silo_query_local_table_device": (ctypes.c_int, [vp, u32, vp, u64, ctypes.POINTER(ctypes.c_int)]),
+        "silo_query_set_table": (ctypes.c_int, [vp, u32, vp, u64]),
+        "silo_query_finish": (vp, [vp, u32]),
+        "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32]),
+        "silo_synth_free": (None, [vp]),
+        "silo_synth_db": (vp, [vp]),
+        "silo_synth_clade_mutation_count": (u32, [vp]),
+        "silo_synth_clade_mutation": (None, [vp, u32, pu32, ctypes.c_char_p]),
+        "silo_synth_lineage_name": (cp, [vp, u32]),
+        "silo_synth_verify_against_builder": (ctypes.c_int64, [vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _host = lib
+    return lib
+
+
+class SiloError(RuntimeError):
+    """code 1 = QueryParseException (HTTP 400 in the reference), 2 = compilation, 3 = anything else (500)."""
+
+    def __init__(self, message):
+        super().__init__(message)
+        kind = message.split(":", 1)[0]
+        self.kind = kind
+        self.message = message.split(":", 1)[1] if ":" in message else message
+
+
+def _error():
+    return SiloError(host().silo_last_error().decode())
+
+
+def _take_string(ptr):
+    if not ptr:
+        raise _error()
+    try:
+        return ctypes.string_at(ptr).decode()
+    finally:
+        host().silo_free(ptr)
+
+
+def _take_ids(ptr, n):
+    try:
+        return np.ctypeslib.as_array(ctypes.cast(ptr, ctypes.POINTER(ctypes.c_uint32)), shape=(max(n, 1),))[:n].copy()
+    finally:
+        host().silo_free(ptr)
+
+
+class Database:
+    """A silo::Database built on the host (dataset directory or synthetic generator)."""
+
+    def __init__(self, handle, owner=None):
+        self.handle = handle
+        self._owner = owner   # synthetic handle that owns the Database
+
+    @classmethod
+    def from_directory(cls, path):
+        h = host().silo_db_build_from_dir(str(path).encode())
+        if not h:
+            raise _error()
+        return cls(h)
+
+    @classmethod
+    def synthetic(cls, n_sequences, seed, with_amino_acids=False, explicit_sequences=False, genome_length=0, n_threads=0,
+                  reference_genomes=None):
+        ref = reference_genomes or ROOT / "tests" / "golden" / "exampleDataset1000Sequences" / "reference_genomes.json"
+        s = host().silo_synth_generate(str(ref).encode(), n_sequences, seed, int(with_amino_acids), int(explicit_sequences), genome_length, n_threads)
+        if not s:
+            raise _error()
+        db = cls(host().silo_synth_db(s), owner=s)
+        return db
+
+    @property
+    def n_partitions(self):
+        return host().silo_db_partition_count(self.handle)
+
+    def partition_rows(self, p):
+        return host().silo_db_partition_rows(self.handle, p)
+
+    def info(self):
+        return json.loads(_take_string(host().silo_db_info_json(self.handle)))
+
+    def clade_mutations(self):
+        out = []
+        if self._owner is None:
+            return out
+        pos, sym = ctypes.c_uint32(), ctypes.create_string_buffer(2)
+        for i in range(host().silo_synth_clade_mutation_count(self._owner)):
+            host().silo_synth_clade_mutation(self._owner, i, ctypes.byref(pos), sym)
+            out.append((pos.value, sym.raw[:1].decode()))
+        return out
+
+    def lineage_names(self):
+        return [host().silo_synth_lineage_name(self._owner, i).decode() for i in range(96)]
+
+    def verify_against_builder(self):
+        d = host().silo_synth_verify_against_builder(self._owner)
+        if d < 0:
+            raise _error()
+        return d
+
+    def close(self):
+        if self._owner is not None:
+            host().silo_synth_free(self._owner)
+        elif self.handle:
+            host().silo_db_free(self.handle)
+        self.handle = None
+        self._owner = None
+
+
+class Engine:
+    """GPU-resident index of (a subset of) the partitions of a Database + query execution."""
+
+    def __init__(self, db, device=0, partitions=None):
+        self.db = db
+        parts = list(partitions) if partitions is not None else []
+        arr = (ctypes.c_uint32 * max(len(parts), 1))(*parts)
+        self.handle = host().silo_engine_create(db.handle, device, arr, len(parts))
+        if not self.handle:
+            raise _error()
+        self.sb = host().silo_engine_handle(self.handle)
+
+    def execute(self, query):
+        q = query if isinstance(query, str) else json.dumps(query)
+        return json.loads(_take_string(host().silo_engine_execute(self.handle, q.encode())))["queryResult"]
+
+    def mutation_counts(self, query, sequence_name, table_len):
+        q = query if isinstance(query, str) else json.dumps(query)
+        out = np.zeros(table_len, dtype=np.uint32)
+        rc = host().silo_engine_mutation_counts(self.handle, q.encode(), sequence_name.encode(), out.ctypes.data, table_len)
+        if rc not in (0, 4):
+            raise _error()
+        return out, rc == 0
+
+    def filter_ids(self, filter_expression, local_partition):
+        f = filter_expression if isinstance(filter_expression, str) else json.dumps(filter_expression)
+        ptr, n = ctypes.c_void_p(), ctypes.c_size_t()
+        if host().silo_engine_filter_ids(self.handle, f.encode(), local_partition, ctypes.byref(ptr), ctypes.byref(n)) != 0:
+            raise _error()
+        return _take_ids(ptr, n.value)
+
+    def close(self):
+        if self.handle:
+            host().silo_engine_free(self.handle)
+            self.handle = None
+
+
+def eval_optree(tree, device=0):
+    """Evaluates a literal operator tree (operator known-answer tests) on the GPU; returns sorted ids."""
+    t = tree if isinstance(tree, str) else json.dumps(tree)
+    ptr, n = ctypes.c_void_p(), ctypes.c_size_t()
+    if host().silo_engine_eval_optree(device, t.encode(), ctypes.byref(ptr), ctypes.byref(n)) != 0:
+        raise _error()
+    return _take_ids(ptr, n.value)
