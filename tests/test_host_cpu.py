@@ -1,0 +1,57 @@
+"""CPU-only checks of the host side and of the C ABI library (no compute calls without a GPU)."""
+import ctypes
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def test_abi_exports_every_declared_symbol(libs):
+    header = (ROOT / "include" / "silo_b200.h").read_text()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(sb_\w+)\(", header, re.M))
+    assert len(declared) >= 18
+    lib = ctypes.CDLL(str(ROOT / "lapis-silo_b200" / "libsilo_b200.so"))
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"libsilo_b200.so does not export {name}"
+
+
+def test_no_cpu_fallback_without_gpu(libs):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    pysilo, _ = libs
+    lib = ctypes.CDLL(str(ROOT / "lapis-silo_b200" / "libsilo_b200.so"))
+    lib.sb_last_error.restype = ctypes.c_char_p
+    db = ctypes.c_void_p()
+    assert lib.sb_db_create(0, 1, ctypes.byref(db)) != 0          # fails loudly, never falls back
+    assert lib.sb_last_error()
+    with pytest.raises(pysilo.SiloError):
+        pysilo.eval_optree({"op": "full", "row_count": 4})
+
+
+def test_synthetic_generator_matches_reference_shaped_builder(synth_small):
+    """generated index == index built from the explicit row strings by the restated
+    SequenceStorePartition::fill / optimizeBitmaps (builder.hpp), bitmap by bitmap, byte by byte"""
+    assert synth_small.n_partitions >= 20
+    assert synth_small.verify_against_builder() == 0
+
+
+def test_synthetic_is_deterministic(libs):
+    pysilo, _ = libs
+    a = pysilo.Database.synthetic(2000, 7, genome_length=2000).info()
+    b = pysilo.Database.synthetic(2000, 7, genome_length=2000, n_threads=3).info()
+    assert a == b
+
+
+def test_oracle_fast_mode_equals_faithful_mode(libs, synth_small):
+    _, oracle = libs
+    query = {"action": {"type": "Mutations", "minProportion": 0.02},
+             "filterExpression": {"type": "Not", "child": {"type": "PangoLineage", "column": "pangoLineage", "value": "B.1.3", "includeSublineages": True}}}
+    slow, ok1 = oracle.mutation_counts(synth_small, query, "main", 16 * 3000, faithful=True)
+    fast, ok2 = oracle.mutation_counts(synth_small, query, "main", 16 * 3000, faithful=False)
+    assert ok1 and ok2 and slow.sum() > 0
+    assert np.array_equal(slow, fast)
+    aa = {"action": {"type": "AminoAcidMutations", "minProportion": 0.02}, "filterExpression": {"type": "True"}}
+    assert oracle.execute(synth_small, aa, faithful=True) == oracle.execute(synth_small, aa, faithful=False)
