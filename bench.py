@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""bench.py — Mutations-action queries/s on synthetic SARS-CoV-2-shaped data (BASELINE.json).
+
+One "step" = one nucleotide Mutations query (minProportion 0.05) under the N-Of filter of BASELINE config
+C3 (3 of 10 clade-defining NucleotideEquals) over the whole database. The database (default 10 M sequences
+x 29,903 nt) is fixed; with N GPUs its DatabasePartitions are sharded over the ranks (strong scaling) and
+the per-rank count tables are summed with an NCCL reduce.
+
+    value  queries/s with the index resident in HBM and the query compiled once: filter kernels + count
+           kernels (+ NCCL reduce), timed with CUDA events on the library's stream, max over ranks
+    e2e    queries/s through the public call a user makes: query JSON in -> result JSON out, i.e.
+           parse, FilterExpression -> Operator compile, plan upload (H2D), kernels, count table download
+           (D2H), thresholds / proportions on the host
+    --impl reference   the CPU restatement of the reference's algorithm (oracle/, all host threads) on a
+           bounded sample of the same workload (the reference itself cannot be built here)
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT / "lapis-silo_b200"))
+
+GENOME_LENGTH = 29903
+SIGMA = 16
+METRIC = "mutations_queries_per_s"
+UNIT = "queries/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=int(os.environ.get("SILO_BENCH_ROWS", 10_000_000)))
+    ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x51100003)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def c3_query(db):
+    clade = db.clade_mutations()
+    picks = [clade[(7 * k) % len(clade)] for k in range(10)]
+    return {"action": {"type": "Mutations", "minProportion": 0.05},
+            "filterExpression": {"type": "N-Of", "numberOfMatchers": 3, "matchExactly": False,
+                                 "children": [{"type": "NucleotideEquals", "position": p + 1, "symbol": s} for p, s in picks]}}
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples during the timed region (B200_PROFILING.md)."""
+    FIELDS = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self.stop, self.thread = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self.stop.set()
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        sm = [float(s[0]) for s in self.samples if s and s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if len(s) > 1 and s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for s in self.samples for i in range(4) if len(s) > 2 + i and s[2 + i].lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(self.samples)}
+
+
+def measured_peak():
+    path = ROOT / "MEASURED_PEAKS.json"
+    if path.exists():
+        return float(json.loads(path.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_sample(db, query, total_rows, budget_s=20.0):
+    """Oracle (CPU restatement, faithful mode, all host threads) on the smallest owned partitions; scaled to the whole
+    database by rows: value = (sample_rows / total_rows) / seconds  [queries/s]."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_bind
+    owned = sorted(db.owned, key=db.partition_rows)
+    cores = os.cpu_count() or 1
+    sample, rows, seconds = [], 0, 0.0
+    for p in owned:
+        sample.append(p)
+        rows += db.partition_rows(p)
+        seconds, _ = oracle_bind.time_query_subset(db, query, sample, faithful=True, threads=cores)
+        if seconds > budget_s / 4 or rows > 0.25 * total_rows:
+            break
+    return {"value": (rows / total_rows) / seconds, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle faithful mode on {len(sample)} smallest partition(s) = {rows} of {total_rows} rows in {seconds:.2f} s, scaled by rows"}, sample
+
+
+def run_reference(args, rank, world):
+    """The reference arm: the CPU restatement of the reference's own algorithm on the host cores."""
+    if rank != 0:
+        return
+    import pysilo
+    t0 = time.time()
+    db = pysilo.Database.synthetic(args.rows, args.seed)
+    query = c3_query(db)
+    base, sample = cpu_sample(db, query, args.rows)
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_bind
+    cores = os.cpu_count() or 1
+    sample_rows = sum(db.partition_rows(p) for p in sample)
+    for _ in range(args.warmup):
+        oracle_bind.time_query_subset(db, query, sample, faithful=True, threads=cores)
+    times = [oracle_bind.time_query_subset(db, query, sample, faithful=True, threads=cores)[0] for _ in range(args.steps)]
+    per_step = sum(times) / len(times)
+    value = (sample_rows / args.rows) / per_step
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": per_step * 1e3 * args.rows / sample_rows, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic", "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt, nucleotide Mutations under N-Of(3 of 10)", "rows": args.rows},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"oracle faithful mode on {len(sample)} smallest partition(s) = {sample_rows} of {args.rows} rows per step, scaled by rows; reference itself not buildable here"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "setup_s": round(time.time() - t0, 1)}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import pysilo
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    t0 = time.time()
+    db = pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank)
+    t_generate = time.time() - t0
+    engine = pysilo.Engine(db, local_rank, db.owned)
+    t_ingest = time.time() - t0 - t_generate
+    query = c3_query(db)
+    query_json = json.dumps(query)
+    table_len = SIGMA * GENOME_LENGTH
+    counts = torch.zeros(table_len, dtype=torch.int32, device=f"cuda:{local_rank}")
+    prepared = pysilo.Prepared(engine, query)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def device_step():
+        prepared.run_device(0, counts.data_ptr(), table_len)      # synchronous on the library's stream
+        if world > 1:
+            dist.reduce(counts, dst=0, op=dist.ReduceOp.SUM)       # uint32 sums are the same bits as int32 sums
+            torch.cuda.synchronize()
+
+    def e2e_step():
+        if world == 1:
+            return engine.execute(query_json)
+        q = pysilo.DistributedQuery(engine, query_json)
+        produced = torch.tensor([int(q.local_table_device(0, counts.data_ptr(), table_len))], dtype=torch.int32, device=counts.device)
+        dist.reduce(counts, dst=0, op=dist.ReduceOp.SUM)
+        dist.all_reduce(produced, op=dist.ReduceOp.MAX)
+        result = None
+        if rank == 0:
+            host = counts.cpu().numpy().view(np.uint32)
+            if int(produced.item()):
+                q.set_table(0, host)
+            result = q.finish()
+        q.close()
+        return result
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+        e2e_step()
+    info = prepared.run_device(0, counts.data_ptr(), table_len, want_bytes=True)
+    local_k1_bytes = info["k1_bytes"]
+    if world > 1:
+        bytes_t = torch.tensor([info["alg_bytes"], info["k1_bytes"]], dtype=torch.int64, device=counts.device)
+        dist.all_reduce(bytes_t)
+        info["alg_bytes"], info["k1_bytes"] = int(bytes_t[0]), int(bytes_t[1])
+
+    with ClockSampler(local_rank) as clocks:
+        # ---- value: device-resident steps, CUDA events on the library's stream, max over ranks ----
+        barrier()
+        pysilo.k1_accumulated(engine, reset=True)
+        launches0 = pysilo.launch_count(engine)
+        pysilo.timer_begin(engine)
+        for _ in range(args.steps):
+            device_step()
+        device_ms = pysilo.timer_end(engine)
+        barrier()
+        launches = pysilo.launch_count(engine) - launches0
+        k1_ms, k1_launches = pysilo.k1_accumulated(engine, reset=True)
+        # ---- e2e: public API with host buffers, wall clock bracketed by barrier + synchronize ----
+        h2d0, d2h0 = pysilo.transfer_bytes(engine)
+        barrier()
+        w0 = time.perf_counter()
+        for _ in range(args.steps):
+            result = e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - w0
+        h2d1, d2h1 = pysilo.transfer_bytes(engine)
+    if world > 1:
+        t = torch.tensor([device_ms, e2e_s], dtype=torch.float64, device=counts.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        device_ms, e2e_s = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_source = measured_peak()
+        k1_avg_ms = k1_ms / max(k1_launches, 1)
+        achieved = local_k1_bytes / (k1_avg_ms * 1e-3) / 1e9 if k1_avg_ms > 0 else 0.0
+        traffic = None
+        traffic_file = ROOT / "profiles" / "k1_traffic.json"
+        if traffic_file.exists():
+            traffic = json.loads(traffic_file.read_text()).get(str(args.rows))
+        stats = pysilo.pool_stats(engine)
+        d2h_extra = table_len * 4 if world > 1 else 0     # torch copies the reduced table down on rank 0
+        line = {
+            "metric": METRIC, "value": args.steps / (device_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": device_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt, nucleotide Mutations under N-Of(3 of 10)", "rows": args.rows,
+                       "partitions": db.n_partitions, "partitions_on_rank0": len(db.owned), "l2": "inputs larger than L2 (container pool streamed once per query)",
+                       "parallelism": f"partitions sharded over {world} GPU(s), NCCL reduce of the count table"},
+            "e2e": {"value": args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps + len(query_json),
+                    "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps + d2h_extra, "ms_per_step": e2e_s * 1e3 / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k1_and_popcount", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "peak_source": peak_source, "algorithmic_bytes_per_launch": local_k1_bytes, "avg_launch_ms": k1_avg_ms,
+                         "share_of_step": k1_avg_ms / (device_ms / args.steps) if device_ms else None},
+            "scan_gb_per_s": info["alg_bytes"] / (device_ms / args.steps * 1e-3) / 1e9,
+            "algorithmic_bytes_per_query": info["alg_bytes"],
+            "clocks": clocks.summary(),
+            "pool": {k: stats[k] for k in ("array_containers", "run_containers", "bitset_containers", "payload_bytes", "directory_bytes", "missing_bytes", "full_table_bytes", "n_work_items")},
+            "result_rows": len(result) if result is not None else None,
+            "setup_s": {"generate": round(t_generate, 1), "ingest": round(t_ingest, 1)},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _ = cpu_sample(db, query, args.rows)
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
+    prepared.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -143,12 +143,23 @@ typedef struct sb_pool_stats {
 } sb_pool_stats;
 int sb_pool_get_stats(const sb_db* db, sb_pool_stats* out);
 /* Algorithmic bytes of sb_mutations for these results: payload+directory of every stored
- * container of the partial partitions, their filters, missing bitmaps of filtered rows, the table. */
+ * container of the partial partitions, their filters, missing bitmaps of filtered rows, the table.
+ * k1_bytes = the share the fused AND-popcount kernel is accountable for (containers + directory + filters). */
 int sb_mutations_algorithmic_bytes(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
-                                   sb_result* const* results, uint64_t* bytes);
+                                   sb_result* const* results, uint64_t* bytes, uint64_t* k1_bytes);
 /* CUDA-event time of the kernels of the last sb_mutations* call on this db, in milliseconds
  * (k1 = fused AND-popcount scan, total = first kernel to last kernel). */
 int sb_last_timing(const sb_db* db, float* k1_ms, float* total_ms, uint32_t* n_launches);
+
+/* Measurement helpers: CUDA events recorded on the db's own stream (torch.cuda.Event would only see
+ * torch's stream), and the number of kernels launched by this db so far. */
+int sb_timer_begin(sb_db* db);
+int sb_timer_end(sb_db* db, float* elapsed_ms);
+int sb_launch_count(const sb_db* db, uint64_t* launches);
+/* Bytes moved by cudaMemcpyAsync on the db's stream so far (plans / PartQuery up, cardinalities / tables down). */
+int sb_transfer_bytes(const sb_db* db, uint64_t* h2d, uint64_t* d2h);
+/* Accumulated CUDA-event time of k1_and_popcount since the last call with reset != 0, and its launch count. */
+int sb_k1_accumulated(sb_db* db, int reset, double* total_ms, uint64_t* launches);
 
 #ifdef __cplusplus
 }

@@ -64,7 +64,9 @@ struct sb_db {
    bool finalized = false;
    std::mutex mutex;
    cudaStream_t stream = nullptr;
-   cudaEvent_t ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr;
+   cudaEvent_t ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr, ev_timer_begin = nullptr, ev_timer_end = nullptr;
+   uint64_t launch_count = 0, k1_launches = 0, h2d_bytes = 0, d2h_bytes = 0;
+   double k1_total_ms = 0;
    bool timing_valid = false, k1_ran = false;
    uint32_t last_launches = 0;
 
@@ -87,7 +89,7 @@ struct sb_db {
    ~sb_db() {
       cudaSetDevice(device);
       for (auto& c : columns) if (c.device) cudaFree(c.device);
-      if (ev_begin) { cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); }
+      if (ev_begin) { cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); cudaEventDestroy(ev_timer_begin); cudaEventDestroy(ev_timer_end); }
       if (stream) cudaStreamDestroy(stream);
    }
 };
@@ -120,6 +122,8 @@ int sb_db_create(int device, uint32_t n_partitions, sb_db** out) {
       SB_CUDA(cudaEventCreate(&db->ev_k1_begin));
       SB_CUDA(cudaEventCreate(&db->ev_k1_end));
       SB_CUDA(cudaEventCreate(&db->ev_end));
+      SB_CUDA(cudaEventCreate(&db->ev_timer_begin));
+      SB_CUDA(cudaEventCreate(&db->ev_timer_end));
       db->stats.n_partitions = n_partitions;
       *out = db.release();
    });

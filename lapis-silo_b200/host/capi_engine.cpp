@@ -25,6 +25,17 @@ struct QueryState {
    std::map<std::string, std::vector<uint32_t>> tables;   // reduced tables handed back by the caller
 };
 
+// A query compiled and lowered once (plans kept): the device-resident replay used for kernel timing.
+struct PreparedQuery {
+   const DeviceDatabase* device_db;
+   Query query;
+   std::vector<operators::OperatorPtr> trees;
+   std::vector<DeviceDatabase::Plan> plans;
+   std::vector<const sb_node*> plan_ptrs;
+   std::vector<uint32_t> plan_sizes, partitions;
+   std::vector<std::string> names;
+};
+
 }  // namespace
 
 extern "C" {
@@ -155,6 +166,54 @@ char* silo_query_finish(void* state_, uint32_t reduced_count) {
       out = capi::dupString(toJson(result).dump());
    });
    return out;
+}
+
+// ---- prepared queries: compile + lower once, replay filter evaluation + action on the device ----
+void* silo_prepared_create(void* engine_, const char* query_json) {
+   PreparedQuery* out = nullptr;
+   capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      auto p = std::make_unique<PreparedQuery>();
+      p->device_db = &engine;
+      p->query = parseQuery(query_json);
+      if (p->query.action.type != ActionType::AGGREGATED) p->names = engine.mutationSequenceNames(p->query.action);
+      p->plans.resize(engine.owned.size());
+      for (uint32_t local = 0; local < engine.owned.size(); ++local) {
+         p->trees.push_back(p->query.filter->compile(engine.db, *engine.db.partitions[engine.owned[local]], filter::AmbiguityMode::NONE));
+         engine.lower(*p->trees.back(), local, p->plans[local]);
+         p->plan_ptrs.push_back(p->plans[local].nodes.data());
+         p->plan_sizes.push_back(static_cast<uint32_t>(p->plans[local].nodes.size()));
+         p->partitions.push_back(local);
+      }
+      out = p.release();
+   });
+   return out;
+}
+void silo_prepared_free(void* prepared) { delete static_cast<PreparedQuery*>(prepared); }
+
+// One device-resident step: filters of all local partitions, then the count table of sequence `name_index`
+// into `device_counts` (device memory). With device_counts == NULL only the filters run (Aggregated).
+// Also reports the algorithmic bytes of the step when `alg_bytes` is given (costs a filter export: not for timed steps).
+int silo_prepared_run_device(void* prepared_, uint32_t name_index, void* device_counts, uint64_t len, uint32_t* aggregated_count,
+                             uint64_t* alg_bytes, uint64_t* k1_bytes) {
+   return capi::guarded([&] {
+      auto& p = *static_cast<PreparedQuery*>(prepared_);
+      DeviceDatabase::EvaluatedFilters filters;
+      filters.handle = p.device_db->handle;
+      filters.partitions = p.partitions;
+      filters.results.assign(p.partitions.size(), nullptr);
+      engine::check(sb_filter_eval_batch(filters.handle, static_cast<uint32_t>(p.partitions.size()), p.partitions.data(), p.plan_ptrs.data(), p.plan_sizes.data(), filters.results.data()));
+      if (aggregated_count) *aggregated_count = p.device_db->aggregatedCount(filters);
+      if (device_counts) {
+         int produced = 0;
+         engine::check(sb_mutations_device(filters.handle, p.names.at(name_index).c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(),
+                                           filters.results.data(), device_counts, len, &produced));
+      }
+      if (alg_bytes) {
+         engine::check(sb_mutations_algorithmic_bytes(filters.handle, p.names.at(name_index).c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(),
+                                                      filters.results.data(), alg_bytes, k1_bytes));
+      }
+   });
 }
 
 }  // extern "C"

@@ -46,6 +46,7 @@ struct Options {
    bool explicit_sequences = false;   // tests only (small n)
    uint32_t n_threads = 0;
    uint32_t genome_length = 0;        // 0 = full reference; otherwise truncate (tests)
+   uint32_t world = 1, rank = 0;      // multi-GPU: build only the partitions this rank owns (the others stay empty shells)
 };
 
 struct Event { uint32_t pos; uint8_t sym; };

@@ -109,6 +109,7 @@ struct Generated {
    // explicit_sequences: per partition, per sequence name, the rows as text (nullopt = NULL genome)
    std::vector<std::map<std::string, std::vector<std::optional<std::string>>>> explicit_sequences;
    std::vector<std::string> lineage_names;
+   std::vector<uint32_t> owned;   // partitions built on this rank (all when world == 1)
    std::vector<std::pair<uint32_t, uint8_t>> clade_mutations;   // (0-based pos, alt) defining substitutions of mid-level lineages (BASELINE config C3)
 };
 
@@ -228,6 +229,25 @@ inline Generated generate(const Options& options, const std::map<std::string, st
    for (const char* r : REGIONS) db.dictionaries["region"]->getOrCreateId(r);
 
    db.partitions.resize(n_partitions);
+   // partition -> rank: longest-processing-time-first on row counts, deterministic on every rank
+   std::vector<uint32_t> rank_of_partition(n_partitions, 0);
+   {
+      std::vector<uint32_t> by_size(n_partitions);
+      for (uint32_t p = 0; p < n_partitions; ++p) by_size[p] = p;
+      std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return partition_rows[a].size() > partition_rows[b].size(); });
+      std::vector<uint64_t> load(std::max<uint32_t>(options.world, 1), 0);
+      for (uint32_t p : by_size) {
+         const uint32_t r = static_cast<uint32_t>(std::min_element(load.begin(), load.end()) - load.begin());
+         rank_of_partition[p] = r;
+         load[r] += partition_rows[p].size();
+      }
+      for (uint32_t p = 0; p < n_partitions; ++p) {
+         if (rank_of_partition[p] == options.rank) { out.owned.push_back(p); continue; }
+         db.partitions[p] = std::make_unique<DatabasePartition>();   // shell: row count only
+         db.partitions[p]->sequence_count = static_cast<uint32_t>(partition_rows[p].size());
+         std::vector<RowMeta>().swap(partition_rows[p]);
+      }
+   }
    out.explicit_sequences.resize(options.explicit_sequences ? n_partitions : 0);
    std::atomic<uint32_t> next_partition{0};
    std::vector<std::string> errors(n_threads);
@@ -236,6 +256,7 @@ inline Generated generate(const Options& options, const std::map<std::string, st
          while (true) {
             const uint32_t p = next_partition.fetch_add(1);
             if (p >= n_partitions) break;
+            if (rank_of_partition[p] != options.rank) continue;
             auto& rows = partition_rows[p];
             std::sort(rows.begin(), rows.end(), [](const RowMeta& a, const RowMeta& b) { return a.date != b.date ? a.date < b.date : a.id < b.id; });   // NULL date (0) first
             auto part = std::make_unique<DatabasePartition>();

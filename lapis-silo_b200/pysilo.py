@@ -60,7 +60,12 @@ def host():
         "silo_query_local_table_device": (ctypes.c_int, [vp, u32, vp, u64, ctypes.POINTER(ctypes.c_int)]),
         "silo_query_set_table": (ctypes.c_int, [vp, u32, vp, u64]),
         "silo_query_finish": (vp, [vp, u32]),
-        "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32]),
+        "silo_prepared_create": (vp, [vp, cp]),
+        "silo_prepared_free": (None, [vp]),
+        "silo_prepared_run_device": (ctypes.c_int, [vp, u32, vp, u64, pu32, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
+        "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32]),
+        "silo_synth_owned_count": (u32, [vp]),
+        "silo_synth_owned": (u32, [vp, u32]),
         "silo_synth_free": (None, [vp]),
         "silo_synth_db": (vp, [vp]),
         "silo_synth_clade_mutation_count": (u32, [vp]),
@@ -112,6 +117,7 @@ class Database:
     def __init__(self, handle, owner=None):
         self.handle = handle
         self._owner = owner   # synthetic handle that owns the Database
+        self.owned = None     # synthetic multi-GPU: partitions built on this rank
 
     @classmethod
     def from_directory(cls, path):
@@ -122,12 +128,13 @@ class Database:
 
     @classmethod
     def synthetic(cls, n_sequences, seed, with_amino_acids=False, explicit_sequences=False, genome_length=0, n_threads=0,
-                  reference_genomes=None):
+                  reference_genomes=None, world=1, rank=0):
         ref = reference_genomes or ROOT / "tests" / "golden" / "exampleDataset1000Sequences" / "reference_genomes.json"
-        s = host().silo_synth_generate(str(ref).encode(), n_sequences, seed, int(with_amino_acids), int(explicit_sequences), genome_length, n_threads)
+        s = host().silo_synth_generate(str(ref).encode(), n_sequences, seed, int(with_amino_acids), int(explicit_sequences), genome_length, n_threads, world, rank)
         if not s:
             raise _error()
         db = cls(host().silo_synth_db(s), owner=s)
+        db.owned = [host().silo_synth_owned(s, i) for i in range(host().silo_synth_owned_count(s))]
         return db
 
     @property
@@ -212,3 +219,127 @@ def eval_optree(tree, device=0):
     if host().silo_engine_eval_optree(device, t.encode(), ctypes.byref(ptr), ctypes.byref(n)) != 0:
         raise _error()
     return _take_ids(ptr, n.value)
+
+
+class PoolStats(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_uint64) for n in (
+        "array_containers", "array_values", "run_containers", "run_values", "run_count", "bitset_containers", "bitset_values",
+        "directory_bytes", "payload_bytes", "missing_bytes", "full_table_bytes", "total_device_bytes",
+        "n_stores", "n_partitions", "n_work_items", "n_chunks")]
+
+
+def _sb():
+    host()
+    lib = ctypes.CDLL(str(PKG / "libsilo_b200.so"))
+    lib.sb_last_error.restype = ctypes.c_char_p
+    for name in ("sb_timer_begin", "sb_timer_end", "sb_launch_count", "sb_k1_accumulated", "sb_pool_get_stats", "sb_transfer_bytes"):
+        getattr(lib, name).restype = ctypes.c_int
+    lib.sb_timer_begin.argtypes = [ctypes.c_void_p]
+    lib.sb_timer_end.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_float)]
+    lib.sb_launch_count.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64)]
+    lib.sb_k1_accumulated.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64)]
+    lib.sb_transfer_bytes.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
+    lib.sb_pool_get_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(PoolStats)]
+    return lib
+
+
+def _sb_check(rc):
+    if rc != 0:
+        raise SiloError("other:" + _sb().sb_last_error().decode())
+
+
+def timer_begin(engine):
+    _sb_check(_sb().sb_timer_begin(engine.sb))
+
+
+def timer_end(engine):
+    ms = ctypes.c_float()
+    _sb_check(_sb().sb_timer_end(engine.sb, ctypes.byref(ms)))
+    return ms.value
+
+
+def launch_count(engine):
+    n = ctypes.c_uint64()
+    _sb_check(_sb().sb_launch_count(engine.sb, ctypes.byref(n)))
+    return n.value
+
+
+def transfer_bytes(engine):
+    a, b = ctypes.c_uint64(), ctypes.c_uint64()
+    _sb_check(_sb().sb_transfer_bytes(engine.sb, ctypes.byref(a), ctypes.byref(b)))
+    return a.value, b.value
+
+
+def k1_accumulated(engine, reset=False):
+    ms, n = ctypes.c_double(), ctypes.c_uint64()
+    _sb_check(_sb().sb_k1_accumulated(engine.sb, int(reset), ctypes.byref(ms), ctypes.byref(n)))
+    return ms.value, n.value
+
+
+def pool_stats(engine):
+    st = PoolStats()
+    _sb_check(_sb().sb_pool_get_stats(engine.sb, ctypes.byref(st)))
+    return {n: getattr(st, n) for n, _ in PoolStats._fields_}
+
+
+class Prepared:
+    """A query compiled and lowered once; run_device() replays filter evaluation + the action on the GPU."""
+
+    def __init__(self, engine, query):
+        q = query if isinstance(query, str) else json.dumps(query)
+        self.engine = engine
+        self.handle = host().silo_prepared_create(engine.handle, q.encode())
+        if not self.handle:
+            raise _error()
+
+    def run_device(self, name_index=0, device_ptr=None, table_len=0, want_bytes=False, want_count=False):
+        count, total, k1 = ctypes.c_uint32(), ctypes.c_uint64(), ctypes.c_uint64()
+        rc = host().silo_prepared_run_device(self.handle, name_index, device_ptr, table_len, ctypes.byref(count) if want_count else None,
+                                            ctypes.byref(total) if want_bytes else None, ctypes.byref(k1) if want_bytes else None)
+        if rc != 0:
+            raise _error()
+        return {"count": count.value, "alg_bytes": total.value, "k1_bytes": k1.value}
+
+    def close(self):
+        if self.handle:
+            host().silo_prepared_free(self.handle)
+            self.handle = None
+
+
+class DistributedQuery:
+    """Multi-GPU protocol (one process per GPU): begin() evaluates the local filters, local tables are written
+    into device memory for an NCCL reduce by the caller, finish() assembles the result on the root rank."""
+
+    def __init__(self, engine, query):
+        q = query if isinstance(query, str) else json.dumps(query)
+        self.handle = host().silo_query_begin(engine.handle, q.encode())
+        if not self.handle:
+            raise _error()
+        self.names = [host().silo_query_sequence_name(self.handle, i).decode() for i in range(host().silo_query_sequence_count(self.handle))]
+
+    def table_len(self, i):
+        return host().silo_query_table_len(self.handle, i)
+
+    def local_count(self):
+        c = ctypes.c_uint32()
+        if host().silo_query_local_count(self.handle, ctypes.byref(c)) != 0:
+            raise _error()
+        return c.value
+
+    def local_table_device(self, i, device_ptr, length):
+        produced = ctypes.c_int()
+        if host().silo_query_local_table_device(self.handle, i, device_ptr, length, ctypes.byref(produced)) != 0:
+            raise _error()
+        return produced.value != 0
+
+    def set_table(self, i, host_array):
+        if host().silo_query_set_table(self.handle, i, host_array.ctypes.data, host_array.size) != 0:
+            raise _error()
+
+    def finish(self, reduced_count=0):
+        return json.loads(_take_string(host().silo_query_finish(self.handle, reduced_count)))["queryResult"]
+
+    def close(self):
+        if self.handle:
+            host().silo_query_free(self.handle)
+            self.handle = None

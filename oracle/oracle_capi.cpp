@@ -1,5 +1,6 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_roaring.hpp). C entry points for ctypes.
 // The `db` arguments are silo::Database* handles created by libsilo_host.so (silo_db_*).
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -37,11 +38,25 @@ void oracle_free(void* p) { free(p); }
 char* oracle_execute_query(const void* db, const char* query_json, int faithful, int threads) {
    char* out = nullptr;
    guarded([&] {
-      oracle::Options options{faithful != 0, static_cast<unsigned>(threads)};
+      oracle::Options options{faithful != 0, static_cast<unsigned>(threads), {}};
       auto result = oracle::executeQuery(*static_cast<const silo::Database*>(db), query_json, options);
       out = dupString(silo::toJson(result).dump());
    });
    return out;
+}
+
+// Bounded sample for the timed CPU baseline: the query restricted to `partitions`; returns seconds of
+// wall-clock spent in executeQuery (filter + action), or a negative value on error.
+double oracle_time_query_subset(const void* db, const char* query_json, int faithful, int threads, const uint32_t* partitions, uint32_t n, uint64_t* result_rows) {
+   double seconds = -1;
+   guarded([&] {
+      oracle::Options options{faithful != 0, static_cast<unsigned>(threads), std::vector<uint32_t>(partitions, partitions + n)};
+      const auto begin = std::chrono::steady_clock::now();
+      auto result = oracle::executeQuery(*static_cast<const silo::Database*>(db), query_json, options);
+      seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - begin).count();
+      if (result_rows) *result_rows = result.query_result.size();
+   });
+   return seconds;
 }
 
 int oracle_eval_optree(const char* optree_json, uint32_t** ids, size_t* n) {
@@ -69,7 +84,7 @@ int oracle_mutation_counts(const void* db_, const char* query_json, const char* 
    int rc = guarded([&] {
       const auto& db = *static_cast<const silo::Database*>(db_);
       std::map<std::string, std::vector<uint32_t>> tables;
-      oracle::Options options{faithful != 0, static_cast<unsigned>(threads)};
+      oracle::Options options{faithful != 0, static_cast<unsigned>(threads), {}};
       oracle::executeQuery(db, query_json, options, &tables);
       memset(out, 0, out_len * sizeof(uint32_t));
       auto it = tables.find(sequence_name);

@@ -307,13 +307,19 @@ inline void addMutationsToOutput(const std::string& sequence_name, const Alphabe
    }
 }
 
-struct Options { bool faithful = true; unsigned threads = 0; };
+struct Options {
+   bool faithful = true;
+   unsigned threads = 0;
+   std::vector<uint32_t> partitions;   // bounded samples: evaluate only these partitions (empty = all), the others count as empty filters
+};
 
 // query_engine.cpp:40-49: serial compile + evaluate per partition
 inline std::vector<OperatorResult> evaluateFilters(const Database& db, const filter::Expression& filter_expression,
-                                                   std::vector<operators::OperatorPtr>* keep_alive) {
+                                                   std::vector<operators::OperatorPtr>* keep_alive, const std::vector<uint32_t>& subset = {}) {
    std::vector<OperatorResult> partition_filters;
-   for (const auto& part : db.partitions) {
+   for (size_t index = 0; index < db.partitions.size(); ++index) {
+      const auto& part = db.partitions[index];
+      if (!subset.empty() && std::find(subset.begin(), subset.end(), index) == subset.end()) { partition_filters.emplace_back(); continue; }
       auto op = filter_expression.compile(db, *part, filter::AmbiguityMode::NONE);
       partition_filters.push_back(evaluate(*op));
       keep_alive->push_back(std::move(op));  // BitmapSelection / IndexScan results may borrow from the tree's sources
@@ -360,7 +366,7 @@ inline QueryResult executeQuery(const Database& db, const std::string& query_str
                                 std::map<std::string, std::vector<uint32_t>>* tables = nullptr) {
    Query query = parseQuery(query_string);
    std::vector<operators::OperatorPtr> trees;
-   std::vector<OperatorResult> filters = evaluateFilters(db, *query.filter, &trees);
+   std::vector<OperatorResult> filters = evaluateFilters(db, *query.filter, &trees, options.partitions);
    return query.action.executeAndOrder([&]() -> QueryResult {
       if (query.action.type == ActionType::AGGREGATED) {
          if (!query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");

@@ -25,6 +25,8 @@ def lib():
         o.oracle_eval_optree.argtypes = [cp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         o.oracle_filter_ids.argtypes = [vp, cp, ctypes.c_uint32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         o.oracle_mutation_counts.argtypes = [vp, cp, cp, ctypes.c_int, ctypes.c_int, vp, ctypes.c_size_t]
+        o.oracle_time_query_subset.restype = ctypes.c_double
+        o.oracle_time_query_subset.argtypes = [vp, cp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint64)]
         _lib = o
     return _lib
 
@@ -77,3 +79,13 @@ def mutation_counts(db, query, sequence_name, table_len, faithful=True, threads=
     if rc not in (0, 4):
         raise _err()
     return out, rc == 0
+
+
+def time_query_subset(db, query, partitions, faithful=True, threads=0):
+    """seconds the CPU restatement needs for `query` restricted to `partitions` (bounded bench sample)"""
+    arr = (ctypes.c_uint32 * max(len(partitions), 1))(*partitions)
+    rows = ctypes.c_uint64()
+    seconds = lib().oracle_time_query_subset(db.handle, json.dumps(query).encode(), int(faithful), threads, arr, len(partitions), ctypes.byref(rows))
+    if seconds < 0:
+        raise _err()
+    return seconds, rows.value
