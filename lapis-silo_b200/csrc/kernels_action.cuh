@@ -12,13 +12,38 @@
 
 namespace sb {
 
-constexpr int K1_THREADS = 256;
-constexpr uint32_t K1_TINY = 8;   // arrays up to this cardinality are handled one per lane
+constexpr int K1_THREADS = 512;    // 16 warps: one chunk of 32 entries per warp per stage
+constexpr uint32_t K1_TINY = 8;    // arrays up to this cardinality: one container per lane, fully unrolled probes
+constexpr uint32_t K1_STAGE_BYTES = STAGE_CHUNKS * 32 * 8 + STAGE_SMALL_U16 * 2 + 128;   // entries + small payload + StageRec
+constexpr uint32_t K1_FILTER_BYTES = SLAB_WORDS32 * 4;
 
 __device__ __forceinline__ uint32_t laneId() { return threadIdx.x & 31; }
 __device__ __forceinline__ uint32_t laneMaskLt() { return (1u << laneId()) - 1u; }
-
 __device__ __forceinline__ int warpSum(int v) { return __reduce_add_sync(0xFFFFFFFFu, v); }
+
+// ---- bulk async copy (TMA 1-D) + mbarrier, sm_90+ PTX ------------------------------------------------
+__device__ __forceinline__ uint32_t smemAddr(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbarInit(uint64_t* bar, uint32_t count) {
+   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbarExpectTx(uint64_t* bar, uint32_t bytes) {
+   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulkLoad(void* dst_smem, const void* src_global, uint32_t bytes, uint64_t* bar) {
+   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                ::"r"(smemAddr(dst_smem)), "l"(src_global), "r"(bytes), "r"(smemAddr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
+   asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "MBAR_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra MBAR_DONE;\n"
+      "bra MBAR_WAIT;\n"
+      "MBAR_DONE:\n"
+      "}\n" ::"r"(smemAddr(bar)), "r"(parity) : "memory");
+}
 
 // Adds `val` to base[idx] once per distinct idx among the lanes with pred set.
 __device__ __forceinline__ void warpAggregatedSharedAdd(uint32_t* base, uint32_t idx, int val, bool pred) {
@@ -41,93 +66,164 @@ __device__ __forceinline__ uint32_t filterRangeCount(const PartQuery& q, uint32_
    return r1 - r0 + __popcll(upto_b) - __popcll(below_a);
 }
 
+// Shared memory of one CTA: [filter slab 32 KB][stage buffer 0][stage buffer 1][tile counts][3 mbarriers].
+// A stage buffer holds the stage's entries (4 KB), its small payload (12 KB) and its StageRec (128 B).
+struct K1Stage {
+   uint64_t entries[STAGE_CHUNKS * 32];
+   uint16_t small[STAGE_SMALL_U16];
+   StageRec rec;
+};
+static_assert(sizeof(K1Stage) == K1_STAGE_BYTES, "stage buffer layout");
+// Large containers (bitsets, big arrays / runs) of the current stage, queued by the lanes that own their
+// entries and then spread over ALL warps of the CTA (a chunk of 32 bitsets must not serialise on one warp).
+struct K1Large { uint32_t offset16; uint32_t meta; uint32_t target; };   // meta: kind | key_local << 2 | size << 4 ; target: slot | deleted << 14 | flipped << 19 | key << 20 (runs)
+constexpr uint32_t K1_LARGE_BYTES = STAGE_CHUNKS * 32 * sizeof(K1Large) + 16;
+
+__device__ __forceinline__ void k1IssueStage(const SeqDev& s, uint32_t stage, K1Stage* buf, uint64_t* bar) {
+   // one thread: read the issue fields of the stage record, then three bulk copies completing on `bar`
+   const uint4 head = __ldg(reinterpret_cast<const uint4*>(s.stages + stage));        // entry_start, n_entries, small_off16 (lo, hi)
+   const uint32_t small_bytes = __ldg(reinterpret_cast<const uint32_t*>(s.stages + stage) + 4);
+   const uint32_t entry_bytes = ((head.y + 1u) & ~1u) * 8u;
+   const uint64_t small_off16 = uint64_t(head.z) | (uint64_t(head.w) << 32);
+   mbarExpectTx(bar, entry_bytes + small_bytes + 128u);
+   bulkLoad(buf->entries, s.entries + head.x, entry_bytes, bar);
+   if (small_bytes) bulkLoad(buf->small, reinterpret_cast<const uint4*>(s.small_pool) + small_off16, small_bytes, bar);
+   bulkLoad(&buf->rec, s.stages + stage, 128u, bar);
+}
+
 __global__ void __launch_bounds__(K1_THREADS)
 k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, uint32_t* __restrict__ counts, int full_mode) {
-   extern __shared__ uint32_t tile_counts[];
+   extern __shared__ __align__(128) uint8_t k1_smem[];
    const WorkItem item = s.items[blockIdx.x];
+   const SlabRec slab = s.slabs[item.slab];
+   const PartQuery q = pq[slab.partition];
+   if (q.state != PART_PARTIAL) return;
+
+   uint32_t* filter_s = reinterpret_cast<uint32_t*>(k1_smem);
+   K1Stage* stage_s = reinterpret_cast<K1Stage*>(k1_smem + K1_FILTER_BYTES);
+   uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES + 2 * K1_STAGE_BYTES);
    const uint32_t tile_slots = s.tile_positions * s.sigma;
-   for (uint32_t i = threadIdx.x; i < tile_slots; i += blockDim.x) tile_counts[i] = 0;
-   __syncthreads();
+   uint64_t* bars = reinterpret_cast<uint64_t*>(tile_counts + tile_slots + (tile_slots & 1));   // [0] filter, [1], [2] stage buffers
+   uint32_t* n_large_s = reinterpret_cast<uint32_t*>(bars + 3);                                  // [0] queue length (16-byte slot)
+   K1Large* large_list = reinterpret_cast<K1Large*>(n_large_s + 4);
 
-   const uint32_t lane = laneId();
-   const uint32_t warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
-   for (uint32_t c = item.chunk_begin + warp; c < item.chunk_end; c += n_warps) {
-      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(s.chunks + c));
-      const uint32_t partition = raw.w & 0xFFFF, n_entries = (raw.w >> 16) & 0xFF;
-      const PartQuery q = pq[partition];
-      if (q.state != PART_PARTIAL) continue;
-      const bool active = lane < n_entries;
-      const uint64_t e = active ? __ldg(s.entries + raw.x + lane) : 0ULL;
-      const uint32_t kind = EntryBits::kind(e), size = EntryBits::size(e), key = EntryBits::key(e);
-      const uint32_t units = !active ? 0u : (kind == KIND_ARRAY ? size : (kind == KIND_RUN ? 2u * size : 0u));
-      uint32_t incl = units;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
-      const uint64_t off = uint64_t(raw.y) * 8ULL + (incl - units);
-      const uint32_t bitset_mask = __ballot_sync(0xFFFFFFFFu, active && kind == KIND_BITSET);
-      const uint32_t bitset_idx = raw.z + __popc(bitset_mask & laneMaskLt());
-      int cnt = 0;
-
-      // (1) tiny arrays: one container per lane, one filter-bit probe per value
-      if (active && kind == KIND_ARRAY && size <= K1_TINY) {
-         const uint16_t* p = s.arrays + off;
-         const uint32_t* f = q.filter32 + key * 2048u;
-#pragma unroll 4
-         for (uint32_t i = 0; i < size; ++i) { const uint32_t v = __ldg(p + i); cnt += (__ldg(f + (v >> 5)) >> (v & 31)) & 1u; }
-      }
-      // (2) larger arrays: the warp strides over one container
-      uint32_t m = __ballot_sync(0xFFFFFFFFu, active && kind == KIND_ARRAY && size > K1_TINY);
-      while (m) {
-         const int l = __ffs(m) - 1; m &= m - 1;
-         const uint64_t o = __shfl_sync(0xFFFFFFFFu, off, l);
-         const uint32_t sz = __shfl_sync(0xFFFFFFFFu, size, l), k = __shfl_sync(0xFFFFFFFFu, key, l);
-         const uint16_t* p = s.arrays + o;
-         const uint32_t* f = q.filter32 + k * 2048u;
-         int c2 = 0;
-         for (uint32_t i = lane; i < sz; i += 32) { const uint32_t v = __ldg(p + i); c2 += (__ldg(f + (v >> 5)) >> (v & 31)) & 1u; }
-         c2 = warpSum(c2);
-         if (int(lane) == l) cnt = c2;
-      }
-      // (3) bitset containers: 128-bit loads of container and filter, AND + popcount
-      m = bitset_mask;
-      while (m) {
-         const int l = __ffs(m) - 1; m &= m - 1;
-         const uint32_t bi = __shfl_sync(0xFFFFFFFFu, bitset_idx, l), k = __shfl_sync(0xFFFFFFFFu, key, l);
-         const uint4* b = s.bitsets + size_t(bi) * 512u;
-         const uint4* f = reinterpret_cast<const uint4*>(q.filter32 + k * 2048u);
-         int c2 = 0;
-#pragma unroll 4
-         for (uint32_t i = lane; i < 512; i += 32) {
-            const uint4 x = __ldg(b + i), y = __ldg(f + i);
-            c2 += __popc(x.x & y.x) + __popc(x.y & y.y) + __popc(x.z & y.z) + __popc(x.w & y.w);
-         }
-         c2 = warpSum(c2);
-         if (int(lane) == l) cnt = c2;
-      }
-      // (4) run containers: two rank lookups per run
-      m = __ballot_sync(0xFFFFFFFFu, active && kind == KIND_RUN);
-      while (m) {
-         const int l = __ffs(m) - 1; m &= m - 1;
-         const uint64_t o = __shfl_sync(0xFFFFFFFFu, off, l);
-         const uint32_t n_runs = __shfl_sync(0xFFFFFFFFu, size, l), k = __shfl_sync(0xFFFFFFFFu, key, l);
-         const uint16_t* p = s.arrays + o;
-         int c2 = 0;
-         for (uint32_t i = lane; i < n_runs; i += 32) {
-            const uint32_t start = __ldg(p + 2 * i), len1 = __ldg(p + 2 * i + 1);
-            c2 += int(filterRangeCount(q, k, start, start + len1));
-         }
-         c2 = warpSum(c2);
-         if (int(lane) == l) cnt = c2;
-      }
-
-      // accumulate: symbol slot, and the deleted symbol of the same (partition, position) (mutations.cpp:90-95)
-      const uint32_t slot = EntryBits::slot(e), deleted = EntryBits::deleted(e);
-      const int add_slot = EntryBits::flipped(e) ? -cnt : cnt;
-      const int add_deleted = full_mode ? -cnt : -add_slot;
-      warpAggregatedSharedAdd(tile_counts, slot, add_slot, active && cnt != 0);
-      warpAggregatedSharedAdd(tile_counts, (slot / s.sigma) * s.sigma + deleted, add_deleted, active && cnt != 0 && deleted != 31u);
+   if (threadIdx.x == 0) {
+      mbarInit(&bars[0], 1); mbarInit(&bars[1], 1); mbarInit(&bars[2], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
    }
    __syncthreads();
+   if (threadIdx.x == 0) {
+      mbarExpectTx(&bars[0], K1_FILTER_BYTES);
+      bulkLoad(filter_s, q.filter32 + size_t(slab.key0) * 2048u, K1_FILTER_BYTES, &bars[0]);
+      k1IssueStage(s, item.stage_begin, &stage_s[0], &bars[1]);
+   }
+   for (uint32_t i = threadIdx.x; i < tile_slots; i += blockDim.x) tile_counts[i] = 0;
+   if (threadIdx.x == 0) { n_large_s[0] = 0; n_large_s[1] = 0; }
+   __syncthreads();
+   mbarWait(&bars[0], 0);
+
+   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
+   const uint4* filter128 = reinterpret_cast<const uint4*>(filter_s);
+   for (uint32_t st = item.stage_begin; st < item.stage_end; ++st) {
+      const uint32_t it = st - item.stage_begin, b = it & 1;
+      if (threadIdx.x == 0) {
+         n_large_s[b ^ 1] = 0;   // the queue counter of the next stage; its last users left at the previous barrier
+         if (st + 1 < item.stage_end) k1IssueStage(s, st + 1, &stage_s[b ^ 1], &bars[1 + (b ^ 1)]);
+      }
+      mbarWait(&bars[1 + b], (it >> 1) & 1);
+      const K1Stage& stage = stage_s[b];
+      const uint32_t n_entries = stage.rec.n_entries;
+      const uint32_t c = warp;                      // chunk of this warp
+      if (c * 32 < n_entries) {
+         const uint32_t idx = c * 32 + lane;
+         const bool active = idx < n_entries;
+         const uint64_t e = active ? stage.entries[idx] : (uint64_t(KIND_NULL) << 30);
+         const uint32_t kind = EntryBits::kind(e), size = EntryBits::size(e), key_local = (EntryBits::key(e) - slab.key0) & (SLAB_KEYS - 1);
+         const uint32_t small_units = EntryBits::smallUnits(kind, size), large_units = EntryBits::largeUnits(kind, size);
+         // warp prefix sums of both payload streams (packed: small in the low half, large in the high half)
+         uint64_t incl = uint64_t(small_units) | (uint64_t(large_units) << 32);
+         const uint64_t own = incl;
+#pragma unroll
+         for (int d = 1; d < 32; d <<= 1) { const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
+         const uint64_t excl = incl - own;
+         const uint16_t* small = stage.small + stage.rec.chunk_small[c] + uint32_t(excl);
+         const uint32_t* f = filter_s + key_local * 2048u;
+         int cnt = 0;
+
+         // (1) tiny arrays: one container per lane, predicated unrolled probes of the shared-memory filter
+         if (kind == KIND_ARRAY && size <= K1_TINY) {
+#pragma unroll
+            for (uint32_t i = 0; i < K1_TINY; ++i) {
+               if (i < size) { const uint32_t v = small[i]; cnt += (f[v >> 5] >> (v & 31)) & 1u; }
+            }
+         } else if (kind == KIND_ARRAY && size <= SMALL_ARRAY_MAX) {   // (2) small arrays: per-lane loop
+            for (uint32_t i = 0; i < size; ++i) { const uint32_t v = small[i]; cnt += (f[v >> 5] >> (v & 31)) & 1u; }
+         } else if (kind == KIND_RUN && size <= SMALL_RUN_MAX) {        // (3) small run containers: rank lookups per run
+            for (uint32_t i = 0; i < size; ++i) { const uint32_t start = small[2 * i], len1 = small[2 * i + 1]; cnt += int(filterRangeCount(q, EntryBits::key(e), start, start + len1)); }
+         }
+         // (4) large containers are queued for the whole CTA
+         if (large_units != 0) {
+            const uint32_t at = atomicAdd(&n_large_s[b], 1u);
+            large_list[at] = {stage.rec.chunk_large[c] + uint32_t(excl >> 32), kind | (key_local << 2) | (size << 4),
+                              EntryBits::slot(e) | (EntryBits::deleted(e) << 14) | (EntryBits::flipped(e) << 19)};
+         }
+
+         // accumulate: symbol slot, and the deleted symbol of the same (partition, position) (mutations.cpp:90-95)
+         const uint32_t slot = EntryBits::slot(e), deleted = EntryBits::deleted(e);
+         const int add_slot = EntryBits::flipped(e) ? -cnt : cnt;
+         const int add_deleted = full_mode ? -cnt : -add_slot;
+         warpAggregatedSharedAdd(tile_counts, slot, add_slot, cnt != 0);
+         warpAggregatedSharedAdd(tile_counts, (slot / s.sigma) * s.sigma + deleted, add_deleted, cnt != 0 && deleted != 31u);
+      }
+      __syncthreads();
+      // phase B: the queued large containers, one per warp at a time, 128-bit loads straight from the large pool
+      const uint32_t n_large = n_large_s[b];
+      if (n_large) {
+         const uint4* large_base = s.large_pool + stage.rec.large_off16;
+         for (uint32_t j = warp; j < n_large; j += blockDim.x >> 5) {
+            const K1Large w = large_list[j];
+            const uint4* src = large_base + w.offset16;
+            const uint32_t k_kind = w.meta & 3u, k_local = (w.meta >> 2) & 3u, k_size = w.meta >> 4;
+            int c2 = 0;
+            if (k_kind == KIND_BITSET) {
+               const uint4* fk = filter128 + k_local * 512u;
+#pragma unroll
+               for (uint32_t half = 0; half < 2; ++half) {
+                  uint4 x[8];
+#pragma unroll
+                  for (uint32_t t = 0; t < 8; ++t) x[t] = __ldg(src + (half * 8 + t) * 32 + lane);
+#pragma unroll
+                  for (uint32_t t = 0; t < 8; ++t) {
+                     const uint4 y = fk[(half * 8 + t) * 32 + lane];
+                     c2 += __popc(x[t].x & y.x) + __popc(x[t].y & y.y) + __popc(x[t].z & y.z) + __popc(x[t].w & y.w);
+                  }
+               }
+            } else if (k_kind == KIND_ARRAY) {
+               const uint32_t* fk = filter_s + k_local * 2048u;
+               for (uint32_t i = lane; i * 8 < k_size; i += 32) {
+                  const uint4 x = __ldg(src + i);
+                  const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                  for (uint32_t t = 0; t < 8; ++t) {
+                     const uint32_t v = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
+                     if (i * 8 + t < k_size) c2 += (fk[v >> 5] >> (v & 31)) & 1u;
+                  }
+               }
+            } else {   // large run container: two rank lookups per run
+               const uint16_t* runs = reinterpret_cast<const uint16_t*>(src);
+               for (uint32_t i = lane; i < k_size; i += 32) { const uint32_t start = __ldg(runs + 2 * i), len1 = __ldg(runs + 2 * i + 1); c2 += int(filterRangeCount(q, slab.key0 + k_local, start, start + len1)); }
+            }
+            c2 = warpSum(c2);
+            if (lane == 0 && c2 != 0) {
+               const uint32_t slot = w.target & 0x3FFFu, deleted = (w.target >> 14) & 31u;
+               const int add_slot = ((w.target >> 19) & 1u) ? -c2 : c2;
+               atomicAdd(&tile_counts[slot], uint32_t(add_slot));
+               if (deleted != 31u) atomicAdd(&tile_counts[(slot / s.sigma) * s.sigma + deleted], uint32_t(full_mode ? -c2 : -add_slot));
+            }
+         }
+      }
+      __syncthreads();   // every warp is done with buffer b (and the queue) before it is refilled
+   }
    // flush: consecutive threads -> consecutive positions of one symbol row of counts[sym][pos]
    const uint32_t tp = s.tile_positions;
    for (uint32_t i = threadIdx.x; i < tile_slots; i += blockDim.x) {

@@ -24,7 +24,7 @@ constexpr int INTERP_STACK = 48;
 struct PlanDesc {
    uint32_t prog_off, prog_len;   // into the program stream
    uint32_t n_words;              // 64-bit words that can hold a set bit (max(row_count, leaf universe))
-   uint32_t n_words_padded;       // multiple of 1024 (whole 65,536-row blocks), zero beyond n_words
+   uint32_t n_words_padded;       // multiple of 4096 (whole 4-key slabs of 262,144 rows), zero beyond n_words
    uint64_t out_off;              // 64-bit word offset of the result in the result slab
    uint64_t rank_local_off;       // uint32 offset
    uint64_t rank_block_off;       // uint32 offset
@@ -81,28 +81,34 @@ __global__ void leaf_position_bitmap(const SeqDev* __restrict__ seqs, const PosL
    const SeqDev& s = seqs[job.seq];
    const uint32_t slots_per_tile = s.tile_positions * s.sigma;
    const uint32_t tile = job.slot / slots_per_tile, slot_local = job.slot - tile * slots_per_tile;
-   const SegRec seg = s.segs[size_t(tile) * s.n_partitions + job.partition];
-   const SegRec next = s.segs[size_t(tile) * s.n_partitions + job.partition + 1];
-   // lower bound of slot_local among the segment's entries
-   uint32_t lo = seg.entry_start, hi = next.entry_start;
-   while (lo < hi) {
-      const uint32_t mid = (lo + hi) >> 1;
-      if (EntryBits::slot(__ldg(s.entries + mid)) < slot_local) lo = mid + 1; else hi = mid;
-   }
    uint64_t* dst = scratch + job.dst_off;
-   for (uint32_t e = lo; e < next.entry_start; ++e) {
-      const uint64_t entry = __ldg(s.entries + e);
-      if (EntryBits::slot(entry) != slot_local) break;
-      const uint32_t chunk_id = seg.chunk_base + ((e - seg.entry_start) >> 5);
-      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(s.chunks + chunk_id));
-      const uint32_t n_entries = (raw.w >> 16) & 0xFF, my = e - raw.x;
-      const uint64_t other = lane < n_entries ? __ldg(s.entries + raw.x + lane) : 0ULL;
-      const uint32_t okind = EntryBits::kind(other);
-      const uint32_t units = lane < my ? (okind == KIND_ARRAY ? EntryBits::size(other) : okind == KIND_RUN ? 2u * EntryBits::size(other) : 0u) : 0u;
-      const uint32_t before = uint32_t(__reduce_add_sync(0xFFFFFFFFu, int(units)));
-      const uint32_t bitsets_before = __popc(__ballot_sync(0xFFFFFFFFu, lane < my && okind == KIND_BITSET));
-      scatterContainer(dst, job.dst_words, EntryBits::key(entry), EntryBits::kind(entry), EntryBits::size(entry),
-                       s.arrays + uint64_t(raw.y) * 8ULL + before, s.bitsets + size_t(raw.z + bitsets_before) * 512u, lane);
+   for (uint32_t slab = s.slab_begin[job.partition]; slab < s.slab_begin[job.partition + 1]; ++slab) {
+      const SegRec seg = s.segs[size_t(tile) * s.n_slabs + slab];
+      const SegRec next = s.segs[size_t(tile) * s.n_slabs + slab + 1];
+      // lower bound of slot_local among the segment's entries (padding entries repeat their predecessor's slot)
+      uint32_t lo = seg.entry_start, hi = next.entry_start;
+      while (lo < hi) {
+         const uint32_t mid = (lo + hi) >> 1;
+         if (EntryBits::slot(__ldg(s.entries + mid)) < slot_local) lo = mid + 1; else hi = mid;
+      }
+      for (uint32_t e = lo; e < next.entry_start; ++e) {
+         const uint64_t entry = __ldg(s.entries + e);
+         if (EntryBits::slot(entry) != slot_local) break;
+         if (EntryBits::kind(entry) == KIND_NULL) continue;
+         // the stage holding entry e: last stage of the segment with entry_start <= e
+         uint32_t a = seg.stage_start, b = next.stage_start;
+         while (b - a > 1) { const uint32_t mid = (a + b) >> 1; if (__ldg(&s.stages[mid].entry_start) <= e) a = mid; else b = mid; }
+         const StageRec* rec = s.stages + a;
+         const uint32_t in_stage = e - __ldg(&rec->entry_start), chunk = in_stage >> 5, my = in_stage & 31;
+         const uint64_t other = lane < my ? __ldg(s.entries + e - my + lane) : (uint64_t(KIND_NULL) << 30);
+         const uint32_t small_before = uint32_t(__reduce_add_sync(0xFFFFFFFFu, int(EntryBits::smallUnits(EntryBits::kind(other), EntryBits::size(other)))));
+         const uint32_t large_before = uint32_t(__reduce_add_sync(0xFFFFFFFFu, int(EntryBits::largeUnits(EntryBits::kind(other), EntryBits::size(other)))));
+         const uint16_t* small = s.small_pool + __ldg(&rec->small_off16) * 8ULL + __ldg(&rec->chunk_small[chunk]) + small_before;
+         const uint4* large = s.large_pool + __ldg(&rec->large_off16) + __ldg(&rec->chunk_large[chunk]) + large_before;
+         const uint32_t kind = EntryBits::kind(entry), size = EntryBits::size(entry);
+         const bool is_small = EntryBits::smallUnits(kind, size) != 0;
+         scatterContainer(dst, job.dst_words, EntryBits::key(entry), kind, size, is_small ? small : reinterpret_cast<const uint16_t*>(large), large, lane);
+      }
    }
 }
 

@@ -106,22 +106,25 @@ struct DeviceBuffer {
 struct Sequence {   // one logical sequence (store name) over all partitions of this db
    std::string name;
    int alphabet = 0;
-   uint32_t length = 0, sigma = 0, tile_positions = 32, n_tiles = 0;
+   uint32_t length = 0, sigma = 0, tile_positions = TILE_POSITIONS, n_tiles = 0;
    std::vector<int> store_of_partition;   // index into Db::stores or -1
    // device
    DeviceBuffer<uint64_t> entries;
-   DeviceBuffer<ChunkRec> chunks;
+   DeviceBuffer<StageRec> stages;
    DeviceBuffer<WorkItem> items;
    DeviceBuffer<SegRec> segs;
-   DeviceBuffer<uint16_t> arrays;
-   DeviceBuffer<uint4> bitsets;
+   DeviceBuffer<SlabRec> slabs;
+   DeviceBuffer<uint32_t> slab_begin;
+   DeviceBuffer<uint16_t> small_pool;
+   DeviceBuffer<uint4> large_pool;
+   std::vector<uint32_t> h_slab_begin;    // [P + 1]
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
    DeviceBuffer<uint64_t> miss_row_base, miss_iv_base;
    DeviceBuffer<uint32_t> full_tables;   // [P][sigma * length]
    SeqDev dev{};
-   uint32_t n_items = 0, n_chunks = 0;
+   uint32_t n_items = 0, n_stages = 0, n_slabs = 0;
    uint64_t n_entries = 0;
 };
 
@@ -129,87 +132,128 @@ struct RegisteredBitmap { uint32_t partition; uint32_t first_container, n_contai
 
 struct Column { uint32_t partition; int dtype; uint32_t n; void* device = nullptr; };
 
-constexpr uint64_t ITEM_WEIGHT_CAP = 256 * 1024;   // bytes of directory + payload per Mutations work item
+constexpr uint64_t ITEM_WEIGHT_CAP = 512 * 1024;   // bytes of directory + payload per Mutations work item
 
 // Packs the ingested stores of one sequence into the tiled device layout.
 inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>& stores, uint32_t n_partitions, sb_pool_stats& stats) {
    const uint32_t sigma = seq.sigma, tp = seq.tile_positions, L = seq.length;
    seq.n_tiles = (L + tp - 1) / tp;
    const uint32_t slots_per_tile = tp * sigma;
+   SB_REQUIRE(slots_per_tile <= 0x4000, "tile does not fit the 14-bit slot field");
+   // slabs: 4 container keys each
+   std::vector<SlabRec> slabs;
+   seq.h_slab_begin.assign(n_partitions + 1, 0);
+   for (uint32_t p = 0; p < n_partitions; ++p) {
+      seq.h_slab_begin[p] = uint32_t(slabs.size());
+      if (seq.store_of_partition[p] < 0) continue;
+      const uint32_t n_rows = stores[seq.store_of_partition[p]]->n_rows;
+      const uint32_t n_keys = std::max<uint32_t>(1, uint32_t((uint64_t(n_rows) + 65535) / 65536));
+      for (uint32_t k = 0; k < n_keys; k += SLAB_KEYS) slabs.push_back({p, k});
+   }
+   seq.h_slab_begin[n_partitions] = uint32_t(slabs.size());
+   const uint32_t n_slabs = uint32_t(slabs.size());
+   seq.n_slabs = n_slabs;
+
    std::vector<uint64_t> entries;
-   std::vector<ChunkRec> chunks;
+   std::vector<StageRec> stage_recs;
    std::vector<WorkItem> items;
-   std::vector<SegRec> segs(size_t(seq.n_tiles) * n_partitions + 1);
-   std::vector<uint16_t> arrays;
-   std::vector<uint64_t> bitsets;   // 1024 words per container
+   std::vector<uint64_t> item_weight;
+   std::vector<SegRec> segs(size_t(seq.n_tiles) * std::max<uint32_t>(n_slabs, 1) + 1);
+   std::vector<uint16_t> small_pool;
+   std::vector<uint64_t> large_pool;   // 16-byte units = 2 words each
    std::vector<size_t> cursor(n_partitions, 0);
    uint64_t total_containers = 0;
    for (uint32_t p = 0; p < n_partitions; ++p) if (seq.store_of_partition[p] >= 0) total_containers += stores[seq.store_of_partition[p]]->containers.size();
-   entries.reserve(total_containers);
+   entries.reserve(total_containers + total_containers / 256 + 16);
+   std::vector<const TmpContainer*> picked;
    for (uint32_t tile = 0; tile < seq.n_tiles; ++tile) {
       const uint32_t slot_end = (tile + 1) * slots_per_tile;
-      const size_t tile_chunk_begin = chunks.size();
-      std::vector<uint64_t> chunk_weight;
-      for (uint32_t p = 0; p < n_partitions; ++p) {
-         segs[size_t(tile) * n_partitions + p] = {uint32_t(entries.size()), uint32_t(chunks.size())};
-         if (seq.store_of_partition[p] < 0) continue;
+      for (uint32_t slab_id = 0; slab_id < n_slabs; ++slab_id) {
+         segs[size_t(tile) * n_slabs + slab_id] = {uint32_t(entries.size()), uint32_t(stage_recs.size())};
+         const uint32_t p = slabs[slab_id].partition, key0 = slabs[slab_id].key0;
          HostStore& st = *stores[seq.store_of_partition[p]];
-         size_t& cur = cursor[p];
-         while (cur < st.containers.size() && st.containers[cur].slot < slot_end) {
-            // open a chunk of up to 32 entries; its payload starts 16-byte aligned
-            while (arrays.size() % 8) arrays.push_back(0);
-            ChunkRec rec{};
+         // the (tile, partition) range of the store's containers; pick this slab's keys, keeping (slot, key) order
+         const size_t begin = cursor[p];
+         size_t end = begin;
+         while (end < st.containers.size() && st.containers[end].slot < slot_end) ++end;
+         if (slab_id + 1 == seq.h_slab_begin[p + 1]) cursor[p] = end;   // last slab of the partition consumes the range
+         picked.clear();
+         for (size_t k = begin; k < end; ++k) if (st.containers[k].key >= key0 && st.containers[k].key < key0 + SLAB_KEYS) picked.push_back(&st.containers[k]);
+         if (picked.empty()) continue;
+         const size_t seg_stage_begin = stage_recs.size();
+         std::vector<uint64_t> stage_weight;
+         size_t k = 0;
+         while (k < picked.size()) {
+            // open a stage: entries start even (the previous stage was padded), small payload starts 16-byte aligned
+            while (small_pool.size() % 8) small_pool.push_back(0);
+            StageRec rec{};
             rec.entry_start = uint32_t(entries.size());
-            SB_REQUIRE(arrays.size() / 8 <= 0xFFFFFFFFull, "array pool exceeds 64 GB");
-            rec.pay_off16 = uint32_t(arrays.size() / 8);
-            rec.bitset_idx = uint32_t(bitsets.size() / 1024);
-            rec.partition = uint16_t(p);
-            uint64_t weight = 16;
-            uint32_t n = 0;
-            while (n < 32 && cur < st.containers.size() && st.containers[cur].slot < slot_end) {
-               const TmpContainer& c = st.containers[cur++];
-               const uint32_t pos = c.slot / sigma, sym = c.slot - pos * sigma;
-               const int8_t del = st.deleted[pos], flip = st.flipped[pos];
-               entries.push_back(EntryBits::pack(c.key, c.slot - tile * slots_per_tile, c.kind, c.kind == KIND_BITSET ? 1 : c.size,
-                                                 del < 0 || uint32_t(del) == sym ? 31u : uint32_t(del), flip >= 0 && uint32_t(flip) == sym));
-               const uint16_t* src = st.payload.data() + c.pay;
-               if (c.kind == KIND_BITSET) {
-                  const uint64_t* w = reinterpret_cast<const uint64_t*>(src);
-                  bitsets.insert(bitsets.end(), w, w + 1024);
-                  weight += 8192 + 8;
-                  stats.bitset_containers++; stats.bitset_values += c.size;
-               } else if (c.kind == KIND_ARRAY) {
-                  arrays.insert(arrays.end(), src, src + c.size);
-                  weight += 2 * c.size + 8;
-                  stats.array_containers++; stats.array_values += c.size;
-               } else {
-                  arrays.insert(arrays.end(), src, src + 2 * c.size);
-                  weight += 4 * c.size + 8;
-                  stats.run_containers++; stats.run_count += c.size;
-                  for (uint32_t r = 0; r < c.size; ++r) stats.run_values += uint64_t(src[2 * r + 1]) + 1;
+            rec.small_off16 = small_pool.size() / 8;
+            rec.large_off16 = large_pool.size() / 2;
+            const size_t small_begin = small_pool.size(), large_begin = large_pool.size() / 2;
+            uint32_t n_chunks = 0, n_entries = 0;
+            while (k < picked.size() && n_chunks < STAGE_CHUNKS && (small_pool.size() - small_begin) + 32 * SMALL_ARRAY_MAX <= STAGE_SMALL_U16) {
+               rec.chunk_small[n_chunks] = uint16_t(small_pool.size() - small_begin);
+               rec.chunk_large[n_chunks] = uint32_t(large_pool.size() / 2 - large_begin);
+               for (uint32_t n = 0; n < 32 && k < picked.size(); ++n, ++k) {
+                  const TmpContainer& c = *picked[k];
+                  const uint32_t pos = c.slot / sigma, sym = c.slot - pos * sigma;
+                  const int8_t del = st.deleted[pos], flip = st.flipped[pos];
+                  entries.push_back(EntryBits::pack(c.key, c.slot - tile * slots_per_tile, c.kind, c.kind == KIND_BITSET ? 1 : c.size,
+                                                    del < 0 || uint32_t(del) == sym ? 31u : uint32_t(del), flip >= 0 && uint32_t(flip) == sym));
+                  ++n_entries;
+                  const uint16_t* src = st.payload.data() + c.pay;
+                  const uint32_t size_field = c.kind == KIND_BITSET ? 1 : c.size;
+                  const uint32_t small_units = EntryBits::smallUnits(c.kind, size_field), large_units = EntryBits::largeUnits(c.kind, size_field);
+                  if (small_units) small_pool.insert(small_pool.end(), src, src + small_units);
+                  else {
+                     const uint32_t n16 = c.kind == KIND_BITSET ? 4096 : c.kind == KIND_ARRAY ? c.size : 2 * c.size;
+                     const size_t at = large_pool.size();
+                     large_pool.resize(at + size_t(large_units) * 2, 0);
+                     memcpy(large_pool.data() + at, src, size_t(n16) * 2);
+                  }
+                  if (c.kind == KIND_BITSET) { stats.bitset_containers++; stats.bitset_values += c.size; }
+                  else if (c.kind == KIND_ARRAY) { stats.array_containers++; stats.array_values += c.size; }
+                  else { stats.run_containers++; stats.run_count += c.size; for (uint32_t r = 0; r < c.size; ++r) stats.run_values += uint64_t(src[2 * r + 1]) + 1; }
                }
-               ++n;
+               ++n_chunks;
             }
-            rec.n_entries = uint8_t(n);
-            chunks.push_back(rec);
-            chunk_weight.push_back(weight);
+            for (uint32_t c = n_chunks; c < STAGE_CHUNKS; ++c) { rec.chunk_small[c] = uint16_t(small_pool.size() - small_begin); rec.chunk_large[c] = uint32_t(large_pool.size() / 2 - large_begin); }
+            while (small_pool.size() % 8) small_pool.push_back(0);
+            rec.n_entries = n_entries;
+            rec.small_bytes = uint32_t((small_pool.size() - small_begin) * 2);
+            stage_recs.push_back(rec);
+            // keep the next stage's entries 16-byte aligned: a padding entry with the slot of its predecessor
+            if (entries.size() % 2) entries.push_back(EntryBits::pack(EntryBits::key(entries.back()), EntryBits::slot(entries.back()), KIND_NULL, 1, 31, 0));
+            stage_weight.push_back(128 + 8ull * n_entries + rec.small_bytes + 16ull * (large_pool.size() / 2 - large_begin));
          }
-      }
-      // cut the tile's chunks into weight-bounded work items
-      size_t begin = tile_chunk_begin;
-      uint64_t acc = 0;
-      for (size_t c = tile_chunk_begin; c < chunks.size(); ++c) {
-         acc += chunk_weight[c - tile_chunk_begin];
-         if (acc >= ITEM_WEIGHT_CAP || c + 1 == chunks.size()) {
-            items.push_back({tile, uint32_t(begin), uint32_t(c + 1), 0});
-            begin = c + 1;
-            acc = 0;
+         // cut the segment's stages into weight-bounded work items
+         size_t item_begin = seg_stage_begin;
+         uint64_t acc = 0;
+         for (size_t sidx = seg_stage_begin; sidx < stage_recs.size(); ++sidx) {
+            acc += stage_weight[sidx - seg_stage_begin];
+            if (acc >= ITEM_WEIGHT_CAP || sidx + 1 == stage_recs.size()) {
+               items.push_back({tile, slab_id, uint32_t(item_begin), uint32_t(sidx + 1)});
+               item_weight.push_back(acc);
+               item_begin = sidx + 1;
+               acc = 0;
+            }
          }
       }
    }
-   segs.back() = {uint32_t(entries.size()), uint32_t(chunks.size())};
+   {  // heaviest items first: the block scheduler hands out CTAs in index order, so the tail stays short
+      std::vector<uint32_t> order(items.size());
+      for (uint32_t k = 0; k < order.size(); ++k) order[k] = k;
+      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_weight[a] > item_weight[b]; });
+      std::vector<WorkItem> sorted(items.size());
+      for (uint32_t k = 0; k < order.size(); ++k) sorted[k] = items[order[k]];
+      items.swap(sorted);
+   }
+   if (entries.size() % 2) entries.push_back(EntryBits::pack(0, 0, KIND_NULL, 1, 31, 0));
+   entries.push_back(EntryBits::pack(0, 0, KIND_NULL, 1, 31, 0));
+   entries.push_back(EntryBits::pack(0, 0, KIND_NULL, 1, 31, 0));
+   segs.back() = {uint32_t(entries.size() - 2), uint32_t(stage_recs.size())};
    SB_REQUIRE(entries.size() < 0xFFFFFFFFull, "more than 2^32 containers in one sequence");
-   // the deleted symbol of an entry must not be the entry's own symbol: handled above (31 = none)
 
    // flags and missing-symbol intervals
    std::vector<int8_t> deleted(size_t(n_partitions) * L, -1), flipped(size_t(n_partitions) * L, -1);
@@ -232,33 +276,35 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
       std::vector<uint2>().swap(st.miss_iv);
       std::vector<uint32_t>().swap(st.miss_row_off);
    }
-   while (arrays.size() % 8) arrays.push_back(0);
+   while (small_pool.size() % 8) small_pool.push_back(0);
    seq.n_entries = entries.size();
    seq.n_items = uint32_t(items.size());
-   seq.n_chunks = uint32_t(chunks.size());
+   seq.n_stages = uint32_t(stage_recs.size());
    seq.entries.upload(entries);
-   seq.chunks.upload(chunks);
+   seq.stages.upload(stage_recs);
    seq.items.upload(items);
    seq.segs.upload(segs);
-   seq.arrays.upload(arrays);
-   seq.bitsets.alloc(bitsets.size() / 2);
-   if (!bitsets.empty()) SB_CUDA(cudaMemcpy(seq.bitsets.ptr, bitsets.data(), bitsets.size() * 8, cudaMemcpyHostToDevice));
+   seq.slabs.upload(slabs);
+   seq.slab_begin.upload(seq.h_slab_begin);
+   seq.small_pool.upload(small_pool);
+   seq.large_pool.alloc(large_pool.size() / 2);
+   if (!large_pool.empty()) SB_CUDA(cudaMemcpy(seq.large_pool.ptr, large_pool.data(), large_pool.size() * 8, cudaMemcpyHostToDevice));
    seq.deleted.upload(deleted);
    seq.flipped.upload(flipped);
    seq.miss_row_off.upload(row_off);
    seq.miss_iv.upload(iv);
    seq.miss_row_base.upload(row_base);
    seq.miss_iv_base.upload(iv_base);
-   stats.directory_bytes += seq.entries.bytes() + seq.chunks.bytes() + seq.items.bytes() + seq.segs.bytes();
-   stats.payload_bytes += seq.arrays.bytes() + seq.bitsets.bytes();
+   stats.directory_bytes += seq.entries.bytes() + seq.stages.bytes() + seq.items.bytes() + seq.segs.bytes() + seq.slabs.bytes();
+   stats.payload_bytes += seq.small_pool.bytes() + seq.large_pool.bytes();
    stats.n_work_items += items.size();
-   stats.n_chunks += chunks.size();
+   stats.n_chunks += stage_recs.size();
    SeqDev& d = seq.dev;
-   d.entries = seq.entries.ptr; d.chunks = seq.chunks.ptr; d.items = seq.items.ptr; d.segs = seq.segs.ptr;
-   d.arrays = seq.arrays.ptr; d.bitsets = seq.bitsets.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
+   d.entries = seq.entries.ptr; d.stages = seq.stages.ptr; d.items = seq.items.ptr; d.segs = seq.segs.ptr; d.slabs = seq.slabs.ptr; d.slab_begin = seq.slab_begin.ptr;
+   d.small_pool = seq.small_pool.ptr; d.large_pool = seq.large_pool.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
    d.miss_row_off = seq.miss_row_off.ptr; d.miss_iv = seq.miss_iv.ptr; d.miss_row_base = seq.miss_row_base.ptr; d.miss_iv_base = seq.miss_iv_base.ptr;
    d.length = L; d.sigma = sigma; d.tile_positions = tp; d.n_tiles = seq.n_tiles; d.n_partitions = n_partitions;
-   d.n_items = seq.n_items; d.n_chunks = seq.n_chunks;
+   d.n_items = seq.n_items; d.n_stages = seq.n_stages; d.n_slabs = n_slabs;
 }
 
 }  // namespace sb

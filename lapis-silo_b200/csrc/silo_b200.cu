@@ -207,6 +207,7 @@ int sb_store_add(sb_db* db, uint32_t partition, const char* name, int alphabet, 
          // the reference never reads the bitmap of the deleted symbol (mutations.cpp:74-83)
          const bool is_deleted = st->deleted[pos] == int(sym);
          parsePortable(blob + b, e - b, [&](const ParsedContainer& c) {
+            SB_REQUIRE(uint64_t(c.key) * 65536 < std::max<uint64_t>(n_rows, 1), "a position bitmap holds row ids beyond sequence_count");
             if (is_deleted) return;
             TmpContainer t{uint32_t(slot), c.key, c.kind, c.kind == KIND_BITSET ? c.card : c.size, st->payload.size()};
             const uint32_t n16 = payloadU16(c);
