@@ -132,6 +132,23 @@ int sb_mutations(sb_db* db, const char* store_name, uint32_t n, const uint32_t* 
 /* Same, but leaves the table in device memory (for an NCCL reduce over NVLink before the copy). */
 int sb_mutations_device(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
                         sb_result* const* results, void* device_counts, size_t counts_len, int* produced);
+/* The selection step of addMutationsToOutput (mutations.cpp:196-215) on the device, so that only the
+ * emitted rows cross PCIe instead of the whole table: for every position, total = sum of the counts of the
+ * `valid` symbols (SymbolType::VALID_MUTATION_SYMBOLS); skipped when 0; threshold = min_proportion == 0 ? 0 :
+ * uint32(ceil(double(total) * min_proportion) - 1) -- the same IEEE double multiply and ceil --; a row for
+ * every valid symbol != reference[position] with count > threshold. Rows come back sorted by (position,
+ * order of `valid`). The proportion double(count) / double(total) stays with the caller. */
+typedef struct sb_mutation_row { uint32_t position, symbol, count, total; } sb_mutation_row;
+/* reference symbols (enum values) of a sequence, one byte per position; needed by the row selection */
+int sb_sequence_set_reference(sb_db* db, const char* store_name, const uint8_t* symbols, uint32_t length);
+/* rows of a count table that already is in device memory (e.g. after an NCCL reduce) */
+int sb_mutation_rows_from_table(sb_db* db, const char* store_name, const void* device_counts, double min_proportion,
+                                const uint8_t* valid, uint32_t n_valid, sb_mutation_row* rows, size_t capacity, size_t* n_rows);
+/* sb_mutations + the selection in one call with one synchronisation; *n_rows may exceed capacity (then call again) */
+int sb_mutations_rows(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions, sb_result* const* results,
+                      double min_proportion, const uint8_t* valid, uint32_t n_valid,
+                      sb_mutation_row* rows, size_t capacity, size_t* n_rows, int* produced);
+
 /* aggregateWithoutGrouping (aggregated.cpp:58-66): sum of cardinalities, uint32 wrap-around. */
 int sb_aggregated_count(sb_db* db, uint32_t n, sb_result* const* results, uint32_t* count);
 

@@ -2,7 +2,9 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cstdint>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -29,6 +31,22 @@ struct Error : std::runtime_error { using std::runtime_error::runtime_error; };
    } while (0)
 
 #define SB_REQUIRE(cond, msg) do { if (!(cond)) throw ::sb::Error(msg); } while (0)
+
+// SB_TRACE=1: host-side lap times of the entry points on stderr (diagnostics only)
+struct Trace {
+   const char* name;
+   bool on;
+   std::chrono::steady_clock::time_point last;
+   std::string text;
+   explicit Trace(const char* n) : name(n), on(getenv("SB_TRACE") != nullptr), last(std::chrono::steady_clock::now()) {}
+   void lap(const char* what) {
+      if (!on) return;
+      const auto now = std::chrono::steady_clock::now();
+      text += std::string(" ") + what + "=" + std::to_string(std::chrono::duration<double, std::micro>(now - last).count()).substr(0, 7);
+      last = now;
+   }
+   ~Trace() { if (on) fprintf(stderr, "[sb] %s:%s\n", name, text.c_str()); }
+};
 
 template <typename F>
 int guarded(F&& f) {

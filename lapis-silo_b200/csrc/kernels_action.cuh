@@ -236,38 +236,45 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, uint32_t* __re
 
 // ---- K2 ---------------------------------------------------------------------------------------------
 constexpr int K2_THREADS = 1024;
-constexpr uint32_t K2_ROWS_PER_BLOCK = 32768;
 constexpr uint32_t K2_MAX_WINDOW = 49152;   // positions per shared-memory difference array (192 KB)
 
-// grid: (row blocks, listed partitions, position windows). `plist` = partitions to process.
+// grid: (row blocks, listed partitions, position windows). `plist` = partitions to process; a block owns
+// `rows_per_block` rows of one partition (the host sizes it so that the grid is about one wave).
 __global__ void __launch_bounds__(K2_THREADS)
 k2_missing(const SeqDev s, const PartQuery* __restrict__ pq, const uint32_t* __restrict__ plist, uint32_t* __restrict__ counts,
-           uint32_t window, int full_mode) {
+           uint32_t window, uint32_t rows_per_block, int full_mode) {
    extern __shared__ int diff[];   // [window + 1]
    __shared__ int warp_sums[32];
-   __shared__ int carry_s;
    __shared__ uint32_t n_filtered_s;
    const uint32_t partition = plist[blockIdx.y];
    const PartQuery q = pq[partition];
-   const uint32_t row0 = blockIdx.x * K2_ROWS_PER_BLOCK;
+   const uint32_t row0 = blockIdx.x * rows_per_block;
    if (row0 >= q.n_rows) return;
-   const uint32_t row1 = min(q.n_rows, row0 + K2_ROWS_PER_BLOCK);
-   const uint32_t w0 = blockIdx.z * window, w1 = min(s.length, w0 + window);
+   const uint32_t row1 = min(q.n_rows, row0 + rows_per_block);
+   const uint32_t w0 = blockIdx.z * window, w1 = min(s.length, w0 + window), width = w1 - w0;
    for (uint32_t i = threadIdx.x; i <= window; i += blockDim.x) diff[i] = 0;
-   if (threadIdx.x == 0) { n_filtered_s = 0; carry_s = 0; }
+   if (threadIdx.x == 0) n_filtered_s = 0;
    __syncthreads();
 
    const uint32_t* row_off = s.miss_row_off + s.miss_row_base[partition];
    const uint2* iv = s.miss_iv + s.miss_iv_base[partition];
    uint32_t local_filtered = 0;
-   for (uint32_t row = row0 + threadIdx.x; row < row1; row += blockDim.x) {
-      if (!((__ldg(q.filter32 + (row >> 5)) >> (row & 31)) & 1u)) continue;
-      ++local_filtered;
-      const uint32_t b = __ldg(row_off + row), e = __ldg(row_off + row + 1);
-      for (uint32_t k = b; k < e; ++k) {
-         const uint2 r = __ldg(iv + k);
-         const uint32_t a = max(r.x, w0), z = min(r.y, w1);
-         if (a < z) { atomicAdd(&diff[a - w0], 1); atomicAdd(&diff[z - w0], -1); }
+   for (uint32_t base = row0 + threadIdx.x; base < row1; base += 4 * K2_THREADS) {   // 4 rows in flight per thread
+      uint32_t b[4], e[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+         const uint32_t row = base + k * K2_THREADS;
+         const bool in = row < row1 && ((__ldg(q.filter32 + (row >> 5)) >> (row & 31)) & 1u);
+         b[k] = e[k] = 0;
+         if (in) { ++local_filtered; b[k] = __ldg(row_off + row); e[k] = __ldg(row_off + row + 1); }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+         for (uint32_t j = b[k]; j < e[k]; ++j) {
+            const uint2 r = __ldg(iv + j);
+            const uint32_t a = max(r.x, w0), z = min(r.y, w1);
+            if (a < z) { atomicAdd(&diff[a - w0], 1); atomicAdd(&diff[z - w0], -1); }
+         }
       }
    }
    local_filtered = uint32_t(warpSum(int(local_filtered)));
@@ -276,37 +283,62 @@ k2_missing(const SeqDev s, const PartQuery* __restrict__ pq, const uint32_t* __r
    const uint32_t n_filtered = n_filtered_s;
    if (n_filtered == 0) return;
 
+   // inclusive scan of diff in place: every thread owns `per` consecutive elements
+   const uint32_t per = (width + K2_THREADS - 1) / K2_THREADS;
+   const uint32_t begin = min(threadIdx.x * per, width), end = min(begin + per, width);
+   int sum = 0;
+   for (uint32_t i = begin; i < end; ++i) sum += diff[i];
+   const uint32_t warp = threadIdx.x >> 5, lane = laneId();
+   int incl = sum;
+#pragma unroll
+   for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
+   if (lane == 31) warp_sums[warp] = incl;
+   __syncthreads();
+   if (warp == 0) {
+      int ws = warp_sums[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, ws, d); if (lane >= uint32_t(d)) ws += t; }
+      warp_sums[lane] = ws;
+   }
+   __syncthreads();
+   int running = incl - sum + (warp ? warp_sums[warp - 1] : 0);
+   for (uint32_t i = begin; i < end; ++i) { running += diff[i]; diff[i] = running; }
+   __syncthreads();
+
    const int8_t* deleted = s.deleted + size_t(partition) * s.length;
    const int8_t* flipped = s.flipped + size_t(partition) * s.length;
-   const uint32_t warp = threadIdx.x >> 5, lane = laneId();
-   for (uint32_t base = 0; base < w1 - w0; base += blockDim.x) {   // blocked inclusive scan of diff
-      const uint32_t i = base + threadIdx.x;
-      int v = i < w1 - w0 ? diff[i] : 0;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, v, d); if (lane >= uint32_t(d)) v += t; }
-      if (lane == 31) warp_sums[warp] = v;
-      __syncthreads();
-      if (warp == 0) {
-         int ws = warp_sums[lane];
-#pragma unroll
-         for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, ws, d); if (lane >= uint32_t(d)) ws += t; }
-         warp_sums[lane] = ws;
+   for (uint32_t i = threadIdx.x; i < width; i += blockDim.x) {   // coalesced over positions
+      const uint32_t pos = w0 + i;
+      const int d = deleted[pos], f = flipped[pos];
+      if (d >= 0) {
+         uint32_t add = n_filtered - uint32_t(diff[i]);          // |F| - #{i in F : pos in M_i}
+         if (f >= 0 && !full_mode) add -= n_filtered;              // deleted -= |F| part of the flipped symbol's count
+         if (add) atomicAdd(counts + size_t(d) * s.length + pos, add);
       }
-      __syncthreads();
-      const int missing = v + (warp ? warp_sums[warp - 1] : 0) + carry_s;
-      if (i < w1 - w0) {
-         const uint32_t pos = w0 + i;
-         const int d = deleted[pos], f = flipped[pos];
-         if (d >= 0) {
-            uint32_t add = n_filtered - uint32_t(missing);          // |F| - #{i in F : pos in M_i}
-            if (f >= 0 && !full_mode) add -= n_filtered;              // deleted -= |F| part of the flipped symbol's count
-            if (add) atomicAdd(counts + size_t(d) * s.length + pos, add);
-         }
-         if (f >= 0) atomicAdd(counts + size_t(f) * s.length + pos, n_filtered);
+      if (f >= 0) atomicAdd(counts + size_t(f) * s.length + pos, n_filtered);
+   }
+}
+
+// ---- row selection (mutations.cpp:196-215) --------------------------------------------------------------
+struct ValidSymbols { uint8_t symbol[32]; uint32_t n; };
+
+__global__ void k4_select_rows(const uint32_t* __restrict__ counts, uint32_t length, const uint8_t* __restrict__ reference, ValidSymbols valid,
+                               double min_proportion, sb_mutation_row* __restrict__ rows, uint32_t capacity, uint32_t* __restrict__ n_rows) {
+   const uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+   if (pos >= length) return;
+   uint32_t total = 0;
+   for (uint32_t k = 0; k < valid.n; ++k) total += counts[size_t(valid.symbol[k]) * length + pos];
+   if (total == 0) return;
+   const uint32_t threshold = min_proportion == 0 ? 0u : static_cast<uint32_t>(ceil(__dmul_rn(static_cast<double>(total), min_proportion)) - 1);
+   const uint32_t ref = reference[pos];
+   for (uint32_t k = 0; k < valid.n; ++k) {
+      const uint32_t sym = valid.symbol[k];
+      if (sym == ref) continue;
+      const uint32_t count = counts[size_t(sym) * length + pos];
+      if (count > threshold) {
+         const uint32_t at = atomicAdd(n_rows, 1u);
+         if (at < capacity) rows[at] = {pos, k, count, total};   // symbol field carries the index into `valid` until sorted on the host
       }
-      __syncthreads();
-      if (threadIdx.x == 0) carry_s += warp_sums[31];
-      __syncthreads();
    }
 }
 

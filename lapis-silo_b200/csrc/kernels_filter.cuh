@@ -31,7 +31,7 @@ struct PlanDesc {
    uint64_t* cardinality;         // device counter
 };
 
-struct PosLeafJob { uint32_t seq, partition, slot, pad; uint64_t dst_off; uint32_t dst_words, pad2; };
+struct PosLeafJob { uint32_t seq, partition, slot, slab; uint64_t dst_off; uint32_t dst_words, pad2; };   // one per (leaf, slab)
 struct RegContainer { uint64_t pay_off; uint32_t size; uint16_t key; uint8_t kind; uint8_t pad; };  // size: array card / #runs
 struct RegLeafJob { uint32_t container; uint32_t dst_words; uint64_t dst_off; };
 struct BselJob { uint32_t seq, partition, value, contains, n_rows, pad; uint64_t dst_off; };
@@ -64,11 +64,17 @@ __device__ __forceinline__ void scatterContainer(uint64_t* dst, uint32_t n_words
          setRangeWarp(dst, n_words, base + start, base + start + len1, lane);
       }
    } else {
-      const uint64_t* src = reinterpret_cast<const uint64_t*>(bitset);
-      for (uint32_t i = lane; i < 1024; i += 32) {
-         const uint32_t w = key * 1024u + i;
-         const uint64_t x = __ldg(src + i);
-         if (w < n_words && x) atomicOr(reinterpret_cast<unsigned long long*>(dst + w), x);
+      // a bitmap has one container per key and every leaf owns its scratch region: plain 128-bit copy
+      if ((key + 1u) * 1024u <= n_words) {
+         uint4* out = reinterpret_cast<uint4*>(dst + size_t(key) * 1024u);
+#pragma unroll 4
+         for (uint32_t i = lane; i < 512; i += 32) out[i] = __ldg(bitset + i);
+      } else {
+         const uint64_t* src = reinterpret_cast<const uint64_t*>(bitset);
+         for (uint32_t i = lane; i < 1024; i += 32) {
+            const uint32_t w = key * 1024u + i;
+            if (w < n_words) dst[w] = __ldg(src + i);
+         }
       }
    }
 }
@@ -82,7 +88,8 @@ __global__ void leaf_position_bitmap(const SeqDev* __restrict__ seqs, const PosL
    const uint32_t slots_per_tile = s.tile_positions * s.sigma;
    const uint32_t tile = job.slot / slots_per_tile, slot_local = job.slot - tile * slots_per_tile;
    uint64_t* dst = scratch + job.dst_off;
-   for (uint32_t slab = s.slab_begin[job.partition]; slab < s.slab_begin[job.partition + 1]; ++slab) {
+   {
+      const uint32_t slab = job.slab;
       const SegRec seg = s.segs[size_t(tile) * s.n_slabs + slab];
       const SegRec next = s.segs[size_t(tile) * s.n_slabs + slab + 1];
       // lower bound of slot_local among the segment's entries (padding entries repeat their predecessor's slot)

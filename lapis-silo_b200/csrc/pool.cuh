@@ -123,6 +123,8 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<uint2> miss_iv;
    DeviceBuffer<uint64_t> miss_row_base, miss_iv_base;
    DeviceBuffer<uint32_t> full_tables;   // [P][sigma * length]
+   DeviceBuffer<uint8_t> reference;      // [length] symbols of the reference sequence (row selection)
+   DeviceBuffer<uint32_t> row_area;      // [4] counter + selected rows
    SeqDev dev{};
    uint32_t n_items = 0, n_stages = 0, n_slabs = 0;
    uint64_t n_entries = 0;

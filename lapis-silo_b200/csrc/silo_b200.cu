@@ -59,7 +59,7 @@ struct sb_result {
 };
 
 struct sb_db {
-   int device = 0;
+   int device = 0, sm_count = 148;
    uint32_t n_partitions = 0;
    bool finalized = false;
    std::mutex mutex;
@@ -116,8 +116,15 @@ int sb_db_create(int device, uint32_t n_partitions, sb_db** out) {
       SB_CUDA(cudaSetDevice(device));
       auto db = std::make_unique<sb_db>();
       db->device = device;
+      SB_CUDA(cudaDeviceGetAttribute(&db->sm_count, cudaDevAttrMultiProcessorCount, device));
       db->n_partitions = n_partitions;
       SB_CUDA(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
+      {  // keep freed result slabs in the stream-ordered pool: a query must not pay for cudaMalloc
+         cudaMemPool_t pool;
+         SB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+         uint64_t threshold = ~0ULL;
+         SB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+      }
       SB_CUDA(cudaEventCreate(&db->ev_begin));
       SB_CUDA(cudaEventCreate(&db->ev_k1_begin));
       SB_CUDA(cudaEventCreate(&db->ev_k1_end));

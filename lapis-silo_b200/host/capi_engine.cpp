@@ -22,7 +22,8 @@ struct QueryState {
    Query query;
    DeviceDatabase::EvaluatedFilters filters;
    std::vector<std::string> names;
-   std::map<std::string, std::vector<uint32_t>> tables;   // reduced tables handed back by the caller
+   std::map<std::string, std::vector<uint32_t>> tables;   // reduced tables handed back by the caller (host memory)
+   std::map<std::string, std::vector<sb_mutation_row>> rows;   // or the rows selected on the device from a reduced device table
 };
 
 // A query compiled and lowered once (plans kept): the device-resident replay used for kernel timing.
@@ -142,6 +143,14 @@ int silo_query_local_table_device(void* state_, uint32_t i, void* device_counts,
 int silo_query_set_table(void* state_, uint32_t i, const uint32_t* counts, uint64_t len) {
    return capi::guarded([&] { auto* s = static_cast<QueryState*>(state_); s->tables[s->names.at(i)].assign(counts, counts + len); });
 }
+// root rank: the reduced table stays in device memory; only the selected rows come back
+int silo_query_set_table_device(void* state_, uint32_t i, const void* device_counts) {
+   return capi::guarded([&] {
+      auto* s = static_cast<QueryState*>(state_);
+      const std::string& name = s->names.at(i);
+      s->device_db->mutationRowsFromTable(name, s->query.action.alphabetId(), device_counts, s->query.action.min_proportion, s->rows[name]);
+   });
+}
 // root rank: assemble the result from the reduced tables / the reduced count
 char* silo_query_finish(void* state_, uint32_t reduced_count) {
    char* out = nullptr;
@@ -157,6 +166,8 @@ char* silo_query_finish(void* state_, uint32_t reduced_count) {
          QueryResult r;
          const int alphabet_id = action.alphabetId();
          for (const auto& name : s->names) {
+            const auto& reference = s->device_db->db.getReferences(alphabet_id).at(name);
+            if (auto rit = s->rows.find(name); rit != s->rows.end()) { DeviceDatabase::addRowsToOutput(name, alphabetById(alphabet_id), reference, rit->second, r.query_result); continue; }
             auto it = s->tables.find(name);
             if (it == s->tables.end()) continue;
             addMutationsToOutput(name, alphabetById(alphabet_id), s->device_db->db.getReferences(alphabet_id).at(name), it->second.data(), action.min_proportion, r.query_result);

@@ -7,6 +7,7 @@
 //   * runs M5/M6 of the Mutations action (thresholds, double division, rows) and Aggregated's row.
 // There is no CPU evaluation of operators here: sb_* failures surface as exceptions.
 #pragma once
+#include <chrono>
 #include <deque>
 #include <unordered_map>
 
@@ -15,6 +16,19 @@
 #include "query.hpp"
 
 namespace silo::engine {
+
+struct HostTrace {   // SB_TRACE=1: lap times of the host side on stderr (diagnostics only)
+   bool on = getenv("SB_TRACE") != nullptr;
+   std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
+   std::string text;
+   void lap(const char* what) {
+      if (!on) return;
+      const auto now = std::chrono::steady_clock::now();
+      text += std::string(" ") + what + "=" + std::to_string(std::chrono::duration<double, std::micro>(now - last).count()).substr(0, 7);
+      last = now;
+   }
+   ~HostTrace() { if (on) fprintf(stderr, "[host] executeQuery:%s\n", text.c_str()); }
+};
 
 struct DeviceError : std::runtime_error { using std::runtime_error::runtime_error; };
 inline void check(int rc) { if (rc != 0) throw DeviceError(std::string("silo_b200: ") + sb_last_error()); }
@@ -41,6 +55,11 @@ class DeviceDatabase {
          for (uint32_t local = 0; local < owned.size(); ++local) ingestPartition(local, *db.partitions.at(owned[local]));
          std::sort(store_ranges.begin(), store_ranges.end(), [](const StoreRange& a, const StoreRange& b) { return a.begin < b.begin; });
          check(sb_db_finalize(handle));
+         if (!owned.empty()) {
+            for (int alphabet_id = 0; alphabet_id < 2; ++alphabet_id) {
+               for (const auto& [name, reference] : db.getReferences(alphabet_id)) check(sb_sequence_set_reference(handle, name.c_str(), reference.data(), static_cast<uint32_t>(reference.size())));
+            }
+         }
       } catch (...) { sb_db_free(handle); handle = nullptr; throw; }
    }
    // Stand-alone operator trees (the reference's operator unit tests): one partition holding the
@@ -173,11 +192,15 @@ class DeviceDatabase {
    EvaluatedFilters evaluateFilter(const filter::Expression& expression) const {
       std::vector<operators::OperatorPtr> trees;
       std::vector<const operators::Operator*> ptrs;
+      HostTrace trace;
       for (uint32_t global : owned) {   // compile per partition (query_engine.cpp:41-46); evaluation is one batched call
          trees.push_back(expression.compile(db, *db.partitions[global], filter::AmbiguityMode::NONE));
          ptrs.push_back(trees.back().get());
       }
-      return evaluateTrees(ptrs);
+      trace.lap("compile");
+      auto out = evaluateTrees(ptrs);
+      trace.lap("lower+eval");
+      return out;
    }
 
    std::vector<std::string> mutationSequenceNames(const Action& action) const {   // mutations.cpp:240-252
@@ -201,6 +224,45 @@ class DeviceDatabase {
       return produced != 0;
    }
 
+   // the rows of addMutationsToOutput selected on the device (mutations.cpp:196-215); false as mutationCounts
+   bool mutationRows(const EvaluatedFilters& filters, const std::string& name, int alphabet_id, double min_proportion, std::vector<sb_mutation_row>& rows) const {
+      const auto& valid = alphabetById(alphabet_id).valid_mutation_symbols;
+      int produced = 0;
+      size_t n = 0;
+      rows.resize(std::max<size_t>(rows.size(), 4096));
+      for (;;) {
+         check(sb_mutations_rows(handle, name.c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(), filters.results.data(), min_proportion,
+                                 valid.data(), static_cast<uint32_t>(valid.size()), rows.data(), rows.size(), &n, &produced));
+         if (n <= rows.size()) break;
+         rows.resize(n);
+      }
+      rows.resize(n);
+      return produced != 0;
+   }
+   void mutationRowsFromTable(const std::string& name, int alphabet_id, const void* device_counts, double min_proportion, std::vector<sb_mutation_row>& rows) const {
+      const auto& valid = alphabetById(alphabet_id).valid_mutation_symbols;
+      size_t n = 0;
+      rows.resize(std::max<size_t>(rows.size(), 4096));
+      for (;;) {
+         check(sb_mutation_rows_from_table(handle, name.c_str(), device_counts, min_proportion, valid.data(), static_cast<uint32_t>(valid.size()), rows.data(), rows.size(), &n));
+         if (n <= rows.size()) break;
+         rows.resize(n);
+      }
+      rows.resize(n);
+   }
+   // the formatting half of addMutationsToOutput (mutations.cpp:207-214)
+   static void addRowsToOutput(const std::string& name, const Alphabet& alphabet, const std::vector<Symbol>& reference, const std::vector<sb_mutation_row>& rows, std::vector<QueryResultEntry>& output) {
+      output.reserve(output.size() + rows.size());
+      for (const auto& row : rows) {
+         QueryResultEntry entry;
+         entry.fields["mutation"] = alphabet.symbolToChar(reference[row.position]) + std::to_string(row.position + 1) + alphabet.symbolToChar(Symbol(row.symbol));
+         entry.fields["sequenceName"] = name;
+         entry.fields["proportion"] = static_cast<double>(row.count) / static_cast<double>(row.total);
+         entry.fields["count"] = static_cast<int32_t>(row.count);
+         output.push_back(std::move(entry));
+      }
+   }
+
    uint32_t aggregatedCount(const EvaluatedFilters& filters) const {
       uint32_t count = 0;
       check(sb_aggregated_count(handle, static_cast<uint32_t>(filters.results.size()), filters.results.data(), &count));
@@ -208,8 +270,11 @@ class DeviceDatabase {
    }
 
    QueryResult executeQuery(const std::string& query_string, std::map<std::string, std::vector<uint32_t>>* tables = nullptr) const {
+      HostTrace trace;
       Query query = parseQuery(query_string);
+      trace.lap("parse");
       EvaluatedFilters filters = evaluateFilter(*query.filter);
+      trace.lap("filter");
       return query.action.executeAndOrder([&]() -> QueryResult {
          if (query.action.type == ActionType::AGGREGATED) {
             if (!query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
@@ -220,10 +285,13 @@ class DeviceDatabase {
          const int alphabet_id = query.action.alphabetId();
          QueryResult result;
          std::vector<uint32_t> counts;
+         std::vector<sb_mutation_row> rows;
          for (const auto& name : mutationSequenceNames(query.action)) {   // mutations.cpp:258-270
-            if (!mutationCounts(filters, name, alphabet_id, counts)) continue;
-            addMutationsToOutput(name, alphabetById(alphabet_id), db.getReferences(alphabet_id).at(name), counts.data(), query.action.min_proportion, result.query_result);
-            if (tables) (*tables)[name] = counts;
+            if (!mutationRows(filters, name, alphabet_id, query.action.min_proportion, rows)) continue;
+            trace.lap("counts+select");
+            addRowsToOutput(name, alphabetById(alphabet_id), db.getReferences(alphabet_id).at(name), rows, result.query_result);
+            trace.lap("rows");
+            if (tables && mutationCounts(filters, name, alphabet_id, counts)) (*tables)[name] = counts;   // the whole table, for the parity tests
          }
          return result;
       });

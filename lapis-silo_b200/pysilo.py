@@ -59,6 +59,7 @@ def host():
         "silo_query_local_count": (ctypes.c_int, [vp, pu32]),
         "silo_query_local_table_device": (ctypes.c_int, [vp, u32, vp, u64, ctypes.POINTER(ctypes.c_int)]),
         "silo_query_set_table": (ctypes.c_int, [vp, u32, vp, u64]),
+        "silo_query_set_table_device": (ctypes.c_int, [vp, u32, vp]),
         "silo_query_finish": (vp, [vp, u32]),
         "silo_prepared_create": (vp, [vp, cp]),
         "silo_prepared_free": (None, [vp]),
@@ -190,6 +191,10 @@ class Engine:
     def execute(self, query):
         q = query if isinstance(query, str) else json.dumps(query)
         return json.loads(_take_string(host().silo_engine_execute(self.handle, q.encode())))["queryResult"]
+
+    def execute_text(self, query_json):
+        """The response body as the reference's HTTP handler writes it ({"queryResult": [...]}), not parsed."""
+        return _take_string(host().silo_engine_execute(self.handle, query_json.encode() if isinstance(query_json, str) else query_json))
 
     def mutation_counts(self, query, sequence_name, table_len):
         q = query if isinstance(query, str) else json.dumps(query)
@@ -334,6 +339,10 @@ class DistributedQuery:
 
     def set_table(self, i, host_array):
         if host().silo_query_set_table(self.handle, i, host_array.ctypes.data, host_array.size) != 0:
+            raise _error()
+
+    def set_table_device(self, i, device_ptr):
+        if host().silo_query_set_table_device(self.handle, i, device_ptr) != 0:
             raise _error()
 
     def finish(self, reduced_count=0):
