@@ -179,6 +179,26 @@ char* silo_query_finish(void* state_, uint32_t reduced_count) {
    return out;
 }
 
+// The root rank's last step with a reduced table in HOST memory and no engine: parse, M5, order, serialise.
+// (What silo_query_finish does after silo_query_set_table; callable without a device for the gloo tests.)
+char* silo_rows_from_table(const void* db_, const char* query_json, const char* sequence_name, const uint32_t* counts, uint64_t len) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      const auto& db = *static_cast<const Database*>(db_);
+      Query query = parseQuery(query_json);
+      const int alphabet_id = query.action.alphabetId();
+      const auto& reference = db.getReferences(alphabet_id).at(sequence_name);
+      if (len != uint64_t(alphabetById(alphabet_id).count) * reference.size()) throw std::runtime_error("count table size mismatch");
+      QueryResult result = query.action.executeAndOrder([&]() -> QueryResult {
+         QueryResult r;
+         addMutationsToOutput(sequence_name, alphabetById(alphabet_id), reference, counts, query.action.min_proportion, r.query_result);
+         return r;
+      });
+      out = capi::dupString(toJson(result).dump());
+   });
+   return out;
+}
+
 // ---- prepared queries: compile + lower once, replay filter evaluation + action on the device ----
 void* silo_prepared_create(void* engine_, const char* query_json) {
    PreparedQuery* out = nullptr;

@@ -61,6 +61,7 @@ def host():
         "silo_query_set_table": (ctypes.c_int, [vp, u32, vp, u64]),
         "silo_query_set_table_device": (ctypes.c_int, [vp, u32, vp]),
         "silo_query_finish": (vp, [vp, u32]),
+        "silo_rows_from_table": (vp, [vp, cp, cp, vp, u64]),
         "silo_prepared_create": (vp, [vp, cp]),
         "silo_prepared_free": (None, [vp]),
         "silo_prepared_run_device": (ctypes.c_int, [vp, u32, vp, u64, pu32, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
@@ -309,6 +310,13 @@ class Prepared:
         if self.handle:
             host().silo_prepared_free(self.handle)
             self.handle = None
+
+
+def rows_from_table(db, query, sequence_name, counts):
+    """Root-rank result assembly from a reduced uint32 table in host memory (no device needed)."""
+    q = query if isinstance(query, str) else json.dumps(query)
+    counts = np.ascontiguousarray(counts, dtype=np.uint32)
+    return json.loads(_take_string(host().silo_rows_from_table(db.handle, q.encode(), sequence_name.encode(), counts.ctypes.data, counts.size)))["queryResult"]
 
 
 class DistributedQuery:

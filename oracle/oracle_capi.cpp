@@ -95,4 +95,23 @@ int oracle_mutation_counts(const void* db_, const char* query_json, const char* 
    return rc ? rc : status;
 }
 
+// The same restricted to `partitions` (the others count as empty filters): the local table of one rank
+// in the world-size-2 tests of the multi-GPU protocol.
+int oracle_mutation_counts_subset(const void* db_, const char* query_json, const char* sequence_name, int faithful, int threads,
+                                  const uint32_t* partitions, uint32_t n, uint32_t* out, size_t out_len) {
+   int status = 0;
+   int rc = guarded([&] {
+      const auto& db = *static_cast<const silo::Database*>(db_);
+      std::map<std::string, std::vector<uint32_t>> tables;
+      oracle::Options options{faithful != 0, static_cast<unsigned>(threads), std::vector<uint32_t>(partitions, partitions + n)};
+      oracle::executeQuery(db, query_json, options, &tables);
+      memset(out, 0, out_len * sizeof(uint32_t));
+      auto it = tables.find(sequence_name);
+      if (it == tables.end()) { status = 4; return; }
+      if (it->second.size() != out_len) throw std::runtime_error("count table size mismatch");
+      memcpy(out, it->second.data(), out_len * sizeof(uint32_t));
+   });
+   return rc ? rc : status;
+}
+
 }  // extern "C"

@@ -25,6 +25,7 @@ def lib():
         o.oracle_eval_optree.argtypes = [cp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         o.oracle_filter_ids.argtypes = [vp, cp, ctypes.c_uint32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         o.oracle_mutation_counts.argtypes = [vp, cp, cp, ctypes.c_int, ctypes.c_int, vp, ctypes.c_size_t]
+        o.oracle_mutation_counts_subset.argtypes = [vp, cp, cp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, vp, ctypes.c_size_t]
         o.oracle_time_query_subset.restype = ctypes.c_double
         o.oracle_time_query_subset.argtypes = [vp, cp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint64)]
         _lib = o
