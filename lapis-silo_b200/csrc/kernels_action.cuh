@@ -12,9 +12,8 @@
 
 namespace sb {
 
-constexpr int K1_THREADS = 512;    // 16 warps: one chunk of 32 entries per warp per stage
-constexpr uint32_t K1_TINY = 8;    // arrays up to this cardinality: one container per lane, fully unrolled probes
-constexpr uint32_t K1_STAGE_BYTES = STAGE_CHUNKS * 32 * 8 + STAGE_SMALL_U16 * 2 + 128;   // entries + small payload + StageRec
+constexpr int K1_THREADS = 256;    // 8 warps; up to 4 CTAs per SM (48-57 KB of shared memory each)
+constexpr int K1_UNROLL = 4;       // 128-bit posting loads in flight per thread
 constexpr uint32_t K1_FILTER_BYTES = SLAB_WORDS32 * 4;
 
 __device__ __forceinline__ uint32_t laneId() { return threadIdx.x & 31; }
@@ -66,171 +65,122 @@ __device__ __forceinline__ uint32_t filterRangeCount(const PartQuery& q, uint32_
    return r1 - r0 + __popcll(upto_b) - __popcll(below_a);
 }
 
-// Shared memory of one CTA: [filter slab 32 KB][stage buffer 0][stage buffer 1][tile counts][3 mbarriers].
-// A stage buffer holds the stage's entries (4 KB), its small payload (12 KB) and its StageRec (128 B).
-struct K1Stage {
-   uint64_t entries[STAGE_CHUNKS * 32];
-   uint16_t small[STAGE_SMALL_U16];
-   StageRec rec;
+// Block -> work item: the items of every partition are contiguous (heaviest first); a query lists the
+// partial partitions as ranges. block_prefix[k] = first block of range k, item_first[k] = its first item.
+struct K1Map {
+   const uint32_t* block_prefix;   // [n_ranges + 1]
+   const uint32_t* item_first;     // [n_ranges]
+   uint32_t n_ranges;
 };
-static_assert(sizeof(K1Stage) == K1_STAGE_BYTES, "stage buffer layout");
-// Large containers (bitsets, big arrays / runs) of the current stage, queued by the lanes that own their
-// entries and then spread over ALL warps of the CTA (a chunk of 32 bitsets must not serialise on one warp).
-struct K1Large { uint32_t offset16; uint32_t meta; uint32_t target; };   // meta: kind | key_local << 2 | size << 4 ; target: slot | deleted << 14 | flipped << 19 | key << 20 (runs)
-constexpr uint32_t K1_LARGE_BYTES = STAGE_CHUNKS * 32 * sizeof(K1Large) + 16;
 
-__device__ __forceinline__ void k1IssueStage(const SeqDev& s, uint32_t stage, K1Stage* buf, uint64_t* bar) {
-   // one thread: read the issue fields of the stage record, then three bulk copies completing on `bar`
-   const uint4 head = __ldg(reinterpret_cast<const uint4*>(s.stages + stage));        // entry_start, n_entries, small_off16 (lo, hi)
-   const uint32_t small_bytes = __ldg(reinterpret_cast<const uint32_t*>(s.stages + stage) + 4);
-   const uint32_t entry_bytes = ((head.y + 1u) & ~1u) * 8u;
-   const uint64_t small_off16 = uint64_t(head.z) | (uint64_t(head.w) << 32);
-   mbarExpectTx(bar, entry_bytes + small_bytes + 128u);
-   bulkLoad(buf->entries, s.entries + head.x, entry_bytes, bar);
-   if (small_bytes) bulkLoad(buf->small, reinterpret_cast<const uint4*>(s.small_pool) + small_off16, small_bytes, bar);
-   bulkLoad(&buf->rec, s.stages + stage, 128u, bar);
-}
-
-__global__ void __launch_bounds__(K1_THREADS)
-k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, uint32_t* __restrict__ counts, int full_mode) {
+// One CTA per work item. Shared memory: [filter slab 32 KB][tile counts (tile_slots + 1 words)][mbarrier].
+// tile_counts[sym * T + pos_in_tile] accumulates the RAW |F AND B[pos][sym]|; the flipped / deleted-symbol
+// arithmetic (mutations.cpp:85-95, 122-133) is linear in it and is applied once per slot in the flush.
+__global__ void __launch_bounds__(K1_THREADS, 4)
+k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map map, uint32_t* __restrict__ counts, int full_mode) {
    extern __shared__ __align__(128) uint8_t k1_smem[];
-   const WorkItem item = s.items[blockIdx.x];
+   uint32_t range = 0;
+   {  // few ranges (partial partitions): binary search in global memory (L2-resident)
+      uint32_t lo = 0, hi = map.n_ranges;
+      while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(map.block_prefix + mid) <= blockIdx.x) lo = mid; else hi = mid; }
+      range = lo;
+   }
+   const WorkItem item = s.items[__ldg(map.item_first + range) + (blockIdx.x - __ldg(map.block_prefix + range))];
    const SlabRec slab = s.slabs[item.slab];
    const PartQuery q = pq[slab.partition];
-   if (q.state != PART_PARTIAL) return;
 
    uint32_t* filter_s = reinterpret_cast<uint32_t*>(k1_smem);
-   K1Stage* stage_s = reinterpret_cast<K1Stage*>(k1_smem + K1_FILTER_BYTES);
-   uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES + 2 * K1_STAGE_BYTES);
-   const uint32_t tile_slots = s.tile_positions * s.sigma;
-   uint64_t* bars = reinterpret_cast<uint64_t*>(tile_counts + tile_slots + (tile_slots & 1));   // [0] filter, [1], [2] stage buffers
-   uint32_t* n_large_s = reinterpret_cast<uint32_t*>(bars + 3);                                  // [0] queue length (16-byte slot)
-   K1Large* large_list = reinterpret_cast<K1Large*>(n_large_s + 4);
+   uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES);
+   const uint32_t T = s.tile_positions, tile_slots = T * s.sigma;
+   uint64_t* bar = reinterpret_cast<uint64_t*>(tile_counts + ((tile_slots + 2) & ~1u));
 
    if (threadIdx.x == 0) {
-      mbarInit(&bars[0], 1); mbarInit(&bars[1], 1); mbarInit(&bars[2], 1);
+      mbarInit(bar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      mbarExpectTx(bar, K1_FILTER_BYTES);
+      bulkLoad(filter_s, q.filter32 + size_t(slab.key0) * 2048u, K1_FILTER_BYTES, bar);
    }
-   __syncthreads();
-   if (threadIdx.x == 0) {
-      mbarExpectTx(&bars[0], K1_FILTER_BYTES);
-      bulkLoad(filter_s, q.filter32 + size_t(slab.key0) * 2048u, K1_FILTER_BYTES, &bars[0]);
-      k1IssueStage(s, item.stage_begin, &stage_s[0], &bars[1]);
-   }
-   for (uint32_t i = threadIdx.x; i < tile_slots; i += blockDim.x) tile_counts[i] = 0;
-   if (threadIdx.x == 0) { n_large_s[0] = 0; n_large_s[1] = 0; }
-   __syncthreads();
-   mbarWait(&bars[0], 0);
+   for (uint32_t i = threadIdx.x; i <= tile_slots; i += K1_THREADS) tile_counts[i] = 0;
+
+   // posting loads do not depend on the filter: issue the first batch before waiting for it
+   const uint4* post4 = reinterpret_cast<const uint4*>(s.postings + item.post_begin);
+   const uint32_t n4 = (item.post_end - item.post_begin + 3u) >> 2;
+   uint4 v[K1_UNROLL];
+   uint32_t i0 = threadIdx.x;
+#pragma unroll
+   for (int k = 0; k < K1_UNROLL; ++k) v[k] = i0 + k * K1_THREADS < n4 ? __ldg(post4 + i0 + k * K1_THREADS) : make_uint4(~0u, ~0u, ~0u, ~0u);
+   __syncthreads();      // counts zeroed, mbarrier initialised
+   mbarWait(bar, 0);
 
    const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
-   const uint4* filter128 = reinterpret_cast<const uint4*>(filter_s);
-   for (uint32_t st = item.stage_begin; st < item.stage_end; ++st) {
-      const uint32_t it = st - item.stage_begin, b = it & 1;
-      if (threadIdx.x == 0) {
-         n_large_s[b ^ 1] = 0;   // the queue counter of the next stage; its last users left at the previous barrier
-         if (st + 1 < item.stage_end) k1IssueStage(s, st + 1, &stage_s[b ^ 1], &bars[1 + (b ^ 1)]);
-      }
-      mbarWait(&bars[1 + b], (it >> 1) & 1);
-      const K1Stage& stage = stage_s[b];
-      const uint32_t n_entries = stage.rec.n_entries;
-      const uint32_t c = warp;                      // chunk of this warp
-      if (c * 32 < n_entries) {
-         const uint32_t idx = c * 32 + lane;
-         const bool active = idx < n_entries;
-         const uint64_t e = active ? stage.entries[idx] : (uint64_t(KIND_NULL) << 30);
-         const uint32_t kind = EntryBits::kind(e), size = EntryBits::size(e), key_local = (EntryBits::key(e) - slab.key0) & (SLAB_KEYS - 1);
-         const uint32_t small_units = EntryBits::smallUnits(kind, size), large_units = EntryBits::largeUnits(kind, size);
-         // warp prefix sums of both payload streams (packed: small in the low half, large in the high half)
-         uint64_t incl = uint64_t(small_units) | (uint64_t(large_units) << 32);
-         const uint64_t own = incl;
+   // (1) large containers: one per warp at a time, 128-bit loads straight from the large pool
+   for (uint32_t j = item.large_begin + warp; j < item.large_end; j += K1_THREADS / 32) {
+      const LargeEntry w = s.large_entries[j];
+      const uint4* src = s.large_pool + w.offset16;
+      const uint32_t k_kind = w.kind(), k_local = w.keyLocal(), k_size = w.size;
+      int c2 = 0;
+      if (k_kind == KIND_BITSET) {
+         const uint4* fk = reinterpret_cast<const uint4*>(filter_s) + k_local * 512u;
 #pragma unroll
-         for (int d = 1; d < 32; d <<= 1) { const uint64_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
-         const uint64_t excl = incl - own;
-         const uint16_t* small = stage.small + stage.rec.chunk_small[c] + uint32_t(excl);
-         const uint32_t* f = filter_s + key_local * 2048u;
-         int cnt = 0;
-
-         // (1) tiny arrays: one container per lane, predicated unrolled probes of the shared-memory filter
-         if (kind == KIND_ARRAY && size <= K1_TINY) {
+         for (uint32_t half = 0; half < 2; ++half) {
+            uint4 x[8];
 #pragma unroll
-            for (uint32_t i = 0; i < K1_TINY; ++i) {
-               if (i < size) { const uint32_t v = small[i]; cnt += (f[v >> 5] >> (v & 31)) & 1u; }
-            }
-         } else if (kind == KIND_ARRAY && size <= SMALL_ARRAY_MAX) {   // (2) small arrays: per-lane loop
-            for (uint32_t i = 0; i < size; ++i) { const uint32_t v = small[i]; cnt += (f[v >> 5] >> (v & 31)) & 1u; }
-         } else if (kind == KIND_RUN && size <= SMALL_RUN_MAX) {        // (3) small run containers: rank lookups per run
-            for (uint32_t i = 0; i < size; ++i) { const uint32_t start = small[2 * i], len1 = small[2 * i + 1]; cnt += int(filterRangeCount(q, EntryBits::key(e), start, start + len1)); }
-         }
-         // (4) large containers are queued for the whole CTA
-         if (large_units != 0) {
-            const uint32_t at = atomicAdd(&n_large_s[b], 1u);
-            large_list[at] = {stage.rec.chunk_large[c] + uint32_t(excl >> 32), kind | (key_local << 2) | (size << 4),
-                              EntryBits::slot(e) | (EntryBits::deleted(e) << 14) | (EntryBits::flipped(e) << 19)};
-         }
-
-         // accumulate: symbol slot, and the deleted symbol of the same (partition, position) (mutations.cpp:90-95)
-         const uint32_t slot = EntryBits::slot(e), deleted = EntryBits::deleted(e);
-         const int add_slot = EntryBits::flipped(e) ? -cnt : cnt;
-         const int add_deleted = full_mode ? -cnt : -add_slot;
-         warpAggregatedSharedAdd(tile_counts, slot, add_slot, cnt != 0);
-         warpAggregatedSharedAdd(tile_counts, (slot / s.sigma) * s.sigma + deleted, add_deleted, cnt != 0 && deleted != 31u);
-      }
-      __syncthreads();
-      // phase B: the queued large containers, one per warp at a time, 128-bit loads straight from the large pool
-      const uint32_t n_large = n_large_s[b];
-      if (n_large) {
-         const uint4* large_base = s.large_pool + stage.rec.large_off16;
-         for (uint32_t j = warp; j < n_large; j += blockDim.x >> 5) {
-            const K1Large w = large_list[j];
-            const uint4* src = large_base + w.offset16;
-            const uint32_t k_kind = w.meta & 3u, k_local = (w.meta >> 2) & 3u, k_size = w.meta >> 4;
-            int c2 = 0;
-            if (k_kind == KIND_BITSET) {
-               const uint4* fk = filter128 + k_local * 512u;
+            for (uint32_t t = 0; t < 8; ++t) x[t] = __ldg(src + (half * 8 + t) * 32 + lane);
 #pragma unroll
-               for (uint32_t half = 0; half < 2; ++half) {
-                  uint4 x[8];
-#pragma unroll
-                  for (uint32_t t = 0; t < 8; ++t) x[t] = __ldg(src + (half * 8 + t) * 32 + lane);
-#pragma unroll
-                  for (uint32_t t = 0; t < 8; ++t) {
-                     const uint4 y = fk[(half * 8 + t) * 32 + lane];
-                     c2 += __popc(x[t].x & y.x) + __popc(x[t].y & y.y) + __popc(x[t].z & y.z) + __popc(x[t].w & y.w);
-                  }
-               }
-            } else if (k_kind == KIND_ARRAY) {
-               const uint32_t* fk = filter_s + k_local * 2048u;
-               for (uint32_t i = lane; i * 8 < k_size; i += 32) {
-                  const uint4 x = __ldg(src + i);
-                  const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-                  for (uint32_t t = 0; t < 8; ++t) {
-                     const uint32_t v = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
-                     if (i * 8 + t < k_size) c2 += (fk[v >> 5] >> (v & 31)) & 1u;
-                  }
-               }
-            } else {   // large run container: two rank lookups per run
-               const uint16_t* runs = reinterpret_cast<const uint16_t*>(src);
-               for (uint32_t i = lane; i < k_size; i += 32) { const uint32_t start = __ldg(runs + 2 * i), len1 = __ldg(runs + 2 * i + 1); c2 += int(filterRangeCount(q, slab.key0 + k_local, start, start + len1)); }
-            }
-            c2 = warpSum(c2);
-            if (lane == 0 && c2 != 0) {
-               const uint32_t slot = w.target & 0x3FFFu, deleted = (w.target >> 14) & 31u;
-               const int add_slot = ((w.target >> 19) & 1u) ? -c2 : c2;
-               atomicAdd(&tile_counts[slot], uint32_t(add_slot));
-               if (deleted != 31u) atomicAdd(&tile_counts[(slot / s.sigma) * s.sigma + deleted], uint32_t(full_mode ? -c2 : -add_slot));
+            for (uint32_t t = 0; t < 8; ++t) {
+               const uint4 y = fk[(half * 8 + t) * 32 + lane];
+               c2 += __popc(x[t].x & y.x) + __popc(x[t].y & y.y) + __popc(x[t].z & y.z) + __popc(x[t].w & y.w);
             }
          }
+      } else if (k_kind == KIND_ARRAY) {
+         const uint32_t* fk = filter_s + k_local * 2048u;
+         for (uint32_t i = lane; i * 8 < k_size; i += 32) {
+            const uint4 x = __ldg(src + i);
+            const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (uint32_t t = 0; t < 8; ++t) {
+               const uint32_t val = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
+               if (i * 8 + t < k_size) c2 += (fk[val >> 5] >> (val & 31)) & 1u;
+            }
+         }
+      } else {   // long run container: two rank lookups per run
+         const uint16_t* runs = reinterpret_cast<const uint16_t*>(src);
+         for (uint32_t i = lane; i < k_size; i += 32) { const uint32_t start = __ldg(runs + 2 * i), len1 = __ldg(runs + 2 * i + 1); c2 += int(filterRangeCount(q, slab.key0 + k_local, start, start + len1)); }
       }
-      __syncthreads();   // every warp is done with buffer b (and the queue) before it is refilled
+      c2 = warpSum(c2);
+      if (lane == 0 && c2 != 0) atomicAdd(&tile_counts[w.slot()], uint32_t(c2));
    }
-   // flush: consecutive threads -> consecutive positions of one symbol row of counts[sym][pos]
-   const uint32_t tp = s.tile_positions;
-   for (uint32_t i = threadIdx.x; i < tile_slots; i += blockDim.x) {
-      const uint32_t sym = i / tp, pl = i - sym * tp;
-      const uint32_t v = tile_counts[pl * s.sigma + sym];
-      const uint32_t pos = item.tile * tp + pl;
-      if (v != 0 && pos < s.length) atomicAdd(counts + size_t(sym) * s.length + pos, v);
+   // (2) postings: probe the shared-memory filter, count hits per slot
+   auto probe = [&](uint32_t p) {
+      if ((filter_s[(p >> 5) & (SLAB_WORDS32 - 1)] >> (p & 31)) & 1u) atomicAdd(&tile_counts[p >> POSTING_ROW_BITS], 1u);
+   };
+   for (; i0 < n4; i0 += K1_UNROLL * K1_THREADS) {
+      uint4 nxt[K1_UNROLL];
+      const uint32_t i1 = i0 + K1_UNROLL * K1_THREADS;
+#pragma unroll
+      for (int k = 0; k < K1_UNROLL; ++k) nxt[k] = i1 + k * K1_THREADS < n4 ? __ldg(post4 + i1 + k * K1_THREADS) : make_uint4(~0u, ~0u, ~0u, ~0u);
+#pragma unroll
+      for (int k = 0; k < K1_UNROLL; ++k) {
+         if (i0 + k * K1_THREADS < n4) { probe(v[k].x); probe(v[k].y); probe(v[k].z); probe(v[k].w); }
+      }
+#pragma unroll
+      for (int k = 0; k < K1_UNROLL; ++k) v[k] = nxt[k];
+   }
+   __syncthreads();
+   // (3) flush: thread = position of the tile; symbol rows of counts[sym][pos] get coalesced REDs
+   for (uint32_t pl = threadIdx.x; pl < T; pl += K1_THREADS) {
+      const uint32_t pos = item.tile * T + pl;
+      if (pos >= s.length) break;
+      const int del = s.deleted[size_t(slab.partition) * s.length + pos], flip = s.flipped[size_t(slab.partition) * s.length + pos];
+      int acc_deleted = 0;
+      for (uint32_t sym = 0; sym < s.sigma; ++sym) {
+         const int raw = int(tile_counts[sym * T + pl]);
+         if (raw == 0 || int(sym) == del) continue;
+         const int add_slot = int(sym) == flip ? -raw : raw;
+         atomicAdd(counts + size_t(sym) * s.length + pos, uint32_t(add_slot));
+         acc_deleted += full_mode ? -raw : -add_slot;
+      }
+      if (del >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(del) * s.length + pos, uint32_t(acc_deleted));
    }
 }
 

@@ -79,42 +79,36 @@ __device__ __forceinline__ void scatterContainer(uint64_t* dst, uint32_t n_words
    }
 }
 
-// one warp per job: finds the containers of (partition, slot) in the sorted directory and scatters them
+// one warp per (leaf, slab): finds the postings and large containers of slot' in the sorted segment and scatters them
 __global__ void leaf_position_bitmap(const SeqDev* __restrict__ seqs, const PosLeafJob* __restrict__ jobs, uint32_t n_jobs, uint64_t* __restrict__ scratch) {
    const uint32_t job_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = laneId();
    if (job_id >= n_jobs) return;
    const PosLeafJob job = jobs[job_id];
    const SeqDev& s = seqs[job.seq];
-   const uint32_t slots_per_tile = s.tile_positions * s.sigma;
-   const uint32_t tile = job.slot / slots_per_tile, slot_local = job.slot - tile * slots_per_tile;
+   const uint32_t pos = job.slot / s.sigma, sym = job.slot - pos * s.sigma;
+   const uint32_t tile = pos / s.tile_positions, slot2 = sym * s.tile_positions + (pos - tile * s.tile_positions);
    uint64_t* dst = scratch + job.dst_off;
-   {
-      const uint32_t slab = job.slab;
-      const SegRec seg = s.segs[size_t(tile) * s.n_slabs + slab];
-      const SegRec next = s.segs[size_t(tile) * s.n_slabs + slab + 1];
-      // lower bound of slot_local among the segment's entries (padding entries repeat their predecessor's slot)
-      uint32_t lo = seg.entry_start, hi = next.entry_start;
-      while (lo < hi) {
-         const uint32_t mid = (lo + hi) >> 1;
-         if (EntryBits::slot(__ldg(s.entries + mid)) < slot_local) lo = mid + 1; else hi = mid;
+   const SegRec seg = s.segs[size_t(tile) * s.n_slabs + job.slab];
+   const SegRec next = s.segs[size_t(tile) * s.n_slabs + job.slab + 1];
+   const uint32_t key0 = s.slabs[job.slab].key0;
+   {  // postings: lower bound of slot2 << 18, then the run of equal slots, lanes strided
+      const uint32_t target = slot2 << POSTING_ROW_BITS;
+      uint32_t lo = seg.post_start, hi = next.post_start;
+      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(s.postings + mid) < target) lo = mid + 1; else hi = mid; }
+      for (uint32_t e = lo + lane; e < next.post_start; e += 32) {
+         const uint32_t p = __ldg(s.postings + e);
+         if ((p >> POSTING_ROW_BITS) != slot2) break;
+         setBit(dst, job.dst_words, (key0 << 16) + (p & POSTING_ROW_MASK));
       }
-      for (uint32_t e = lo; e < next.entry_start; ++e) {
-         const uint64_t entry = __ldg(s.entries + e);
-         if (EntryBits::slot(entry) != slot_local) break;
-         if (EntryBits::kind(entry) == KIND_NULL) continue;
-         // the stage holding entry e: last stage of the segment with entry_start <= e
-         uint32_t a = seg.stage_start, b = next.stage_start;
-         while (b - a > 1) { const uint32_t mid = (a + b) >> 1; if (__ldg(&s.stages[mid].entry_start) <= e) a = mid; else b = mid; }
-         const StageRec* rec = s.stages + a;
-         const uint32_t in_stage = e - __ldg(&rec->entry_start), chunk = in_stage >> 5, my = in_stage & 31;
-         const uint64_t other = lane < my ? __ldg(s.entries + e - my + lane) : (uint64_t(KIND_NULL) << 30);
-         const uint32_t small_before = uint32_t(__reduce_add_sync(0xFFFFFFFFu, int(EntryBits::smallUnits(EntryBits::kind(other), EntryBits::size(other)))));
-         const uint32_t large_before = uint32_t(__reduce_add_sync(0xFFFFFFFFu, int(EntryBits::largeUnits(EntryBits::kind(other), EntryBits::size(other)))));
-         const uint16_t* small = s.small_pool + __ldg(&rec->small_off16) * 8ULL + __ldg(&rec->chunk_small[chunk]) + small_before;
-         const uint4* large = s.large_pool + __ldg(&rec->large_off16) + __ldg(&rec->chunk_large[chunk]) + large_before;
-         const uint32_t kind = EntryBits::kind(entry), size = EntryBits::size(entry);
-         const bool is_small = EntryBits::smallUnits(kind, size) != 0;
-         scatterContainer(dst, job.dst_words, EntryBits::key(entry), kind, size, is_small ? small : reinterpret_cast<const uint16_t*>(large), large, lane);
+   }
+   {  // large containers of the slot
+      uint32_t lo = seg.large_start, hi = next.large_start;
+      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (s.large_entries[mid].slot() < slot2) lo = mid + 1; else hi = mid; }
+      for (uint32_t e = lo; e < next.large_start; ++e) {
+         const LargeEntry w = s.large_entries[e];
+         if (w.slot() != slot2) break;
+         const uint4* pay = s.large_pool + w.offset16;
+         scatterContainer(dst, job.dst_words, key0 + w.keyLocal(), w.kind(), w.size, reinterpret_cast<const uint16_t*>(pay), pay, lane);
       }
    }
 }

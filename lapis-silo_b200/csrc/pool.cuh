@@ -109,15 +109,15 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    uint32_t length = 0, sigma = 0, tile_positions = TILE_POSITIONS, n_tiles = 0;
    std::vector<int> store_of_partition;   // index into Db::stores or -1
    // device
-   DeviceBuffer<uint64_t> entries;
-   DeviceBuffer<StageRec> stages;
+   DeviceBuffer<uint32_t> postings;
+   DeviceBuffer<LargeEntry> large_entries;
    DeviceBuffer<WorkItem> items;
    DeviceBuffer<SegRec> segs;
    DeviceBuffer<SlabRec> slabs;
    DeviceBuffer<uint32_t> slab_begin;
-   DeviceBuffer<uint16_t> small_pool;
    DeviceBuffer<uint4> large_pool;
    std::vector<uint32_t> h_slab_begin;    // [P + 1]
+   std::vector<uint32_t> h_item_begin;    // [P + 1] work items of each partition (items are ordered by partition, then weight)
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
@@ -126,22 +126,22 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<uint8_t> reference;      // [length] symbols of the reference sequence (row selection)
    DeviceBuffer<uint32_t> row_area;      // [4] counter + selected rows
    SeqDev dev{};
-   uint32_t n_items = 0, n_stages = 0, n_slabs = 0;
-   uint64_t n_entries = 0;
+   uint32_t n_items = 0, n_slabs = 0;
+   uint64_t n_postings = 0, n_large = 0;
 };
 
 struct RegisteredBitmap { uint32_t partition; uint32_t first_container, n_containers; uint32_t max_value; };
 
 struct Column { uint32_t partition; int dtype; uint32_t n; void* device = nullptr; };
 
-constexpr uint64_t ITEM_WEIGHT_CAP = 512 * 1024;   // bytes of directory + payload per Mutations work item
+constexpr uint64_t ITEM_WEIGHT_CAP = 256 * 1024;   // bytes of postings + large payload per Mutations work item
 
 // Packs the ingested stores of one sequence into the tiled device layout.
 inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>& stores, uint32_t n_partitions, sb_pool_stats& stats) {
    const uint32_t sigma = seq.sigma, tp = seq.tile_positions, L = seq.length;
    seq.n_tiles = (L + tp - 1) / tp;
    const uint32_t slots_per_tile = tp * sigma;
-   SB_REQUIRE(slots_per_tile <= 0x4000, "tile does not fit the 14-bit slot field");
+   SB_REQUIRE(slots_per_tile < 0x4000, "tile does not fit the 14-bit slot field (one value is the dummy slot)");
    // slabs: 4 container keys each
    std::vector<SlabRec> slabs;
    seq.h_slab_begin.assign(n_partitions + 1, 0);
@@ -156,106 +156,105 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    const uint32_t n_slabs = uint32_t(slabs.size());
    seq.n_slabs = n_slabs;
 
-   std::vector<uint64_t> entries;
-   std::vector<StageRec> stage_recs;
+   std::vector<uint32_t> postings;
+   std::vector<LargeEntry> large_entries;
    std::vector<WorkItem> items;
    std::vector<uint64_t> item_weight;
    std::vector<SegRec> segs(size_t(seq.n_tiles) * std::max<uint32_t>(n_slabs, 1) + 1);
-   std::vector<uint16_t> small_pool;
    std::vector<uint64_t> large_pool;   // 16-byte units = 2 words each
    std::vector<size_t> cursor(n_partitions, 0);
    uint64_t total_containers = 0;
    for (uint32_t p = 0; p < n_partitions; ++p) if (seq.store_of_partition[p] >= 0) total_containers += stores[seq.store_of_partition[p]]->containers.size();
-   entries.reserve(total_containers + total_containers / 256 + 16);
-   std::vector<const TmpContainer*> picked;
+   postings.reserve(total_containers * 4);
+   struct Picked { uint32_t slot2; const TmpContainer* c; };
+   std::vector<Picked> picked;
+   uint64_t hist[16] = {};   // SB_TRACE: array cardinalities 1,2,3,4,<=8,<=16,<=32,<=64,<=256,<=4096 | runs | bitsets
+   const uint32_t filler = slots_per_tile << POSTING_ROW_BITS;
    for (uint32_t tile = 0; tile < seq.n_tiles; ++tile) {
       const uint32_t slot_end = (tile + 1) * slots_per_tile;
       for (uint32_t slab_id = 0; slab_id < n_slabs; ++slab_id) {
-         segs[size_t(tile) * n_slabs + slab_id] = {uint32_t(entries.size()), uint32_t(stage_recs.size())};
+         while (postings.size() % 4) postings.push_back(filler);
+         segs[size_t(tile) * n_slabs + slab_id] = {uint32_t(postings.size()), uint32_t(large_entries.size())};
          const uint32_t p = slabs[slab_id].partition, key0 = slabs[slab_id].key0;
          HostStore& st = *stores[seq.store_of_partition[p]];
-         // the (tile, partition) range of the store's containers; pick this slab's keys, keeping (slot, key) order
+         // the (tile, partition) range of the store's containers; pick this slab's keys, order by (slot', key)
          const size_t begin = cursor[p];
          size_t end = begin;
          while (end < st.containers.size() && st.containers[end].slot < slot_end) ++end;
          if (slab_id + 1 == seq.h_slab_begin[p + 1]) cursor[p] = end;   // last slab of the partition consumes the range
          picked.clear();
-         for (size_t k = begin; k < end; ++k) if (st.containers[k].key >= key0 && st.containers[k].key < key0 + SLAB_KEYS) picked.push_back(&st.containers[k]);
+         for (size_t k = begin; k < end; ++k) {
+            const TmpContainer& c = st.containers[k];
+            if (c.key < key0 || c.key >= key0 + SLAB_KEYS) continue;
+            const uint32_t local = c.slot - tile * slots_per_tile, pl = local / sigma, sym = local - pl * sigma;
+            picked.push_back({sym * tp + pl, &c});
+         }
          if (picked.empty()) continue;
-         const size_t seg_stage_begin = stage_recs.size();
-         std::vector<uint64_t> stage_weight;
-         size_t k = 0;
-         while (k < picked.size()) {
-            // open a stage: entries start even (the previous stage was padded), small payload starts 16-byte aligned
-            while (small_pool.size() % 8) small_pool.push_back(0);
-            StageRec rec{};
-            rec.entry_start = uint32_t(entries.size());
-            rec.small_off16 = small_pool.size() / 8;
-            rec.large_off16 = large_pool.size() / 2;
-            const size_t small_begin = small_pool.size(), large_begin = large_pool.size() / 2;
-            uint32_t n_chunks = 0, n_entries = 0;
-            while (k < picked.size() && n_chunks < STAGE_CHUNKS && (small_pool.size() - small_begin) + 32 * SMALL_ARRAY_MAX <= STAGE_SMALL_U16) {
-               rec.chunk_small[n_chunks] = uint16_t(small_pool.size() - small_begin);
-               rec.chunk_large[n_chunks] = uint32_t(large_pool.size() / 2 - large_begin);
-               for (uint32_t n = 0; n < 32 && k < picked.size(); ++n, ++k) {
-                  const TmpContainer& c = *picked[k];
-                  const uint32_t pos = c.slot / sigma, sym = c.slot - pos * sigma;
-                  const int8_t del = st.deleted[pos], flip = st.flipped[pos];
-                  entries.push_back(EntryBits::pack(c.key, c.slot - tile * slots_per_tile, c.kind, c.kind == KIND_BITSET ? 1 : c.size,
-                                                    del < 0 || uint32_t(del) == sym ? 31u : uint32_t(del), flip >= 0 && uint32_t(flip) == sym));
-                  ++n_entries;
-                  const uint16_t* src = st.payload.data() + c.pay;
-                  const uint32_t size_field = c.kind == KIND_BITSET ? 1 : c.size;
-                  const uint32_t small_units = EntryBits::smallUnits(c.kind, size_field), large_units = EntryBits::largeUnits(c.kind, size_field);
-                  if (small_units) small_pool.insert(small_pool.end(), src, src + small_units);
-                  else {
-                     const uint32_t n16 = c.kind == KIND_BITSET ? 4096 : c.kind == KIND_ARRAY ? c.size : 2 * c.size;
-                     const size_t at = large_pool.size();
-                     large_pool.resize(at + size_t(large_units) * 2, 0);
-                     memcpy(large_pool.data() + at, src, size_t(n16) * 2);
-                  }
-                  if (c.kind == KIND_BITSET) { stats.bitset_containers++; stats.bitset_values += c.size; }
-                  else if (c.kind == KIND_ARRAY) { stats.array_containers++; stats.array_values += c.size; }
-                  else { stats.run_containers++; stats.run_count += c.size; for (uint32_t r = 0; r < c.size; ++r) stats.run_values += uint64_t(src[2 * r + 1]) + 1; }
-               }
-               ++n_chunks;
-            }
-            for (uint32_t c = n_chunks; c < STAGE_CHUNKS; ++c) { rec.chunk_small[c] = uint16_t(small_pool.size() - small_begin); rec.chunk_large[c] = uint32_t(large_pool.size() / 2 - large_begin); }
-            while (small_pool.size() % 8) small_pool.push_back(0);
-            rec.n_entries = n_entries;
-            rec.small_bytes = uint32_t((small_pool.size() - small_begin) * 2);
-            stage_recs.push_back(rec);
-            // keep the next stage's entries 16-byte aligned: a padding entry with the slot of its predecessor
-            if (entries.size() % 2) entries.push_back(EntryBits::pack(EntryBits::key(entries.back()), EntryBits::slot(entries.back()), KIND_NULL, 1, 31, 0));
-            stage_weight.push_back(128 + 8ull * n_entries + rec.small_bytes + 16ull * (large_pool.size() / 2 - large_begin));
-         }
-         // cut the segment's stages into weight-bounded work items
-         size_t item_begin = seg_stage_begin;
-         uint64_t acc = 0;
-         for (size_t sidx = seg_stage_begin; sidx < stage_recs.size(); ++sidx) {
-            acc += stage_weight[sidx - seg_stage_begin];
-            if (acc >= ITEM_WEIGHT_CAP || sidx + 1 == stage_recs.size()) {
-               items.push_back({tile, slab_id, uint32_t(item_begin), uint32_t(sidx + 1)});
-               item_weight.push_back(acc);
-               item_begin = sidx + 1;
-               acc = 0;
+         std::stable_sort(picked.begin(), picked.end(), [](const Picked& a, const Picked& b) { return a.slot2 < b.slot2; });   // keys stay ascending inside a slot
+         const size_t post_begin = postings.size(), large_begin = large_entries.size();
+         uint64_t large_bytes = 0;
+         for (const Picked& pk : picked) {
+            const TmpContainer& c = *pk.c;
+            const uint16_t* src = st.payload.data() + c.pay;
+            const uint32_t key_local = c.key - key0;
+            uint64_t cardinality = c.size;
+            if (c.kind == KIND_RUN) { cardinality = 0; for (uint32_t r = 0; r < c.size; ++r) cardinality += uint64_t(src[2 * r + 1]) + 1; }
+            if (c.kind == KIND_ARRAY) hist[c.size <= 4 ? c.size - 1 : c.size <= 8 ? 4 : c.size <= 16 ? 5 : c.size <= 32 ? 6 : c.size <= 64 ? 7 : c.size <= 256 ? 8 : 9]++;
+            else hist[c.kind == KIND_RUN ? 10 : 11]++;
+            if (c.kind == KIND_BITSET) { stats.bitset_containers++; stats.bitset_values += c.size; }
+            else if (c.kind == KIND_ARRAY) { stats.array_containers++; stats.array_values += c.size; }
+            else { stats.run_containers++; stats.run_count += c.size; stats.run_values += cardinality; }
+            const uint32_t head = (pk.slot2 << POSTING_ROW_BITS) | (key_local << 16);
+            if (c.kind == KIND_ARRAY && cardinality <= FLAT_MAX) {
+               for (uint32_t i = 0; i < c.size; ++i) postings.push_back(head | src[i]);
+            } else if (c.kind == KIND_RUN && cardinality <= FLAT_MAX) {
+               for (uint32_t r = 0; r < c.size; ++r) for (uint32_t v = src[2 * r], last = uint32_t(src[2 * r]) + src[2 * r + 1]; v <= last; ++v) postings.push_back(head | v);
+            } else {
+               const uint32_t n16 = c.kind == KIND_BITSET ? 4096 : c.kind == KIND_ARRAY ? c.size : 2 * c.size;
+               const size_t at = large_pool.size();
+               SB_REQUIRE(at / 2 < 0xFFFFFFFFull, "large pool beyond 64 GB");
+               large_pool.resize(at + size_t((n16 + 7) / 8) * 2, 0);
+               memcpy(large_pool.data() + at, src, size_t(n16) * 2);
+               large_entries.push_back({uint32_t(at / 2), c.size, pk.slot2 | (uint32_t(c.kind) << 14) | (key_local << 16), 0});
+               large_bytes += 16 + uint64_t((n16 + 7) / 8) * 16;
             }
          }
+         // cut the segment into weight-bounded work items: postings and large entries are split evenly
+         const size_t n_post = postings.size() - post_begin, n_large = large_entries.size() - large_begin;
+         const uint64_t weight = 4ull * n_post + large_bytes;
+         const uint32_t n_cuts = uint32_t(std::max<uint64_t>(1, (weight + ITEM_WEIGHT_CAP - 1) / ITEM_WEIGHT_CAP));
+         for (uint32_t cut = 0; cut < n_cuts; ++cut) {
+            auto postCut = [&](uint32_t c) { return c == n_cuts ? n_post : (n_post * c / n_cuts) & ~size_t(3); };
+            const size_t pb = postCut(cut), pe = postCut(cut + 1), lb = n_large * cut / n_cuts, le = n_large * (cut + 1) / n_cuts;
+            if (pb == pe && lb == le) continue;
+            items.push_back({tile, slab_id, uint32_t(post_begin + pb), uint32_t(post_begin + pe), uint32_t(large_begin + lb), uint32_t(large_begin + le), {0, 0}});
+            item_weight.push_back(4ull * (pe - pb) + (n_large ? large_bytes * (le - lb) / n_large : 0));
+         }
+         SB_REQUIRE(postings.size() < 0xFFFFFFF0ull, "more than 2^32 postings in one sequence");
       }
    }
-   {  // heaviest items first: the block scheduler hands out CTAs in index order, so the tail stays short
+   {  // order: partition, then heaviest first (the block scheduler hands out CTAs in index order, so the tail stays short)
       std::vector<uint32_t> order(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) order[k] = k;
-      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_weight[a] > item_weight[b]; });
+      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+         const uint32_t pa = slabs[items[a].slab].partition, pb = slabs[items[b].slab].partition;
+         return pa != pb ? pa < pb : item_weight[a] > item_weight[b];
+      });
       std::vector<WorkItem> sorted(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) sorted[k] = items[order[k]];
       items.swap(sorted);
+      seq.h_item_begin.assign(n_partitions + 1, 0);
+      for (const WorkItem& it : items) seq.h_item_begin[slabs[it.slab].partition + 1]++;
+      for (uint32_t p = 0; p < n_partitions; ++p) seq.h_item_begin[p + 1] += seq.h_item_begin[p];
    }
-   if (entries.size() % 2) entries.push_back(EntryBits::pack(0, 0, KIND_NULL, 1, 31, 0));
-   entries.push_back(EntryBits::pack(0, 0, KIND_NULL, 1, 31, 0));
-   entries.push_back(EntryBits::pack(0, 0, KIND_NULL, 1, 31, 0));
-   segs.back() = {uint32_t(entries.size() - 2), uint32_t(stage_recs.size())};
-   SB_REQUIRE(entries.size() < 0xFFFFFFFFull, "more than 2^32 containers in one sequence");
+   while (postings.size() % 4) postings.push_back(filler);
+   segs.back() = {uint32_t(postings.size()), uint32_t(large_entries.size())};
+   for (int k = 0; k < 4; ++k) postings.push_back(filler);
+   if (getenv("SB_TRACE")) {
+      fprintf(stderr, "[sb] pack '%s': arrays by cardinality 1:%llu 2:%llu 3:%llu 4:%llu <=8:%llu <=16:%llu <=32:%llu <=64:%llu <=256:%llu <=4096:%llu runs:%llu bitsets:%llu postings:%zu large:%zu items:%zu\n", seq.name.c_str(),
+              (unsigned long long)hist[0], (unsigned long long)hist[1], (unsigned long long)hist[2], (unsigned long long)hist[3], (unsigned long long)hist[4], (unsigned long long)hist[5], (unsigned long long)hist[6],
+              (unsigned long long)hist[7], (unsigned long long)hist[8], (unsigned long long)hist[9], (unsigned long long)hist[10], (unsigned long long)hist[11], postings.size(), large_entries.size(), items.size());
+   }
 
    // flags and missing-symbol intervals
    std::vector<int8_t> deleted(size_t(n_partitions) * L, -1), flipped(size_t(n_partitions) * L, -1);
@@ -278,17 +277,15 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
       std::vector<uint2>().swap(st.miss_iv);
       std::vector<uint32_t>().swap(st.miss_row_off);
    }
-   while (small_pool.size() % 8) small_pool.push_back(0);
-   seq.n_entries = entries.size();
+   seq.n_postings = postings.size();
+   seq.n_large = large_entries.size();
    seq.n_items = uint32_t(items.size());
-   seq.n_stages = uint32_t(stage_recs.size());
-   seq.entries.upload(entries);
-   seq.stages.upload(stage_recs);
+   seq.postings.upload(postings);
+   seq.large_entries.upload(large_entries);
    seq.items.upload(items);
    seq.segs.upload(segs);
    seq.slabs.upload(slabs);
    seq.slab_begin.upload(seq.h_slab_begin);
-   seq.small_pool.upload(small_pool);
    seq.large_pool.alloc(large_pool.size() / 2);
    if (!large_pool.empty()) SB_CUDA(cudaMemcpy(seq.large_pool.ptr, large_pool.data(), large_pool.size() * 8, cudaMemcpyHostToDevice));
    seq.deleted.upload(deleted);
@@ -297,16 +294,16 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.miss_iv.upload(iv);
    seq.miss_row_base.upload(row_base);
    seq.miss_iv_base.upload(iv_base);
-   stats.directory_bytes += seq.entries.bytes() + seq.stages.bytes() + seq.items.bytes() + seq.segs.bytes() + seq.slabs.bytes();
-   stats.payload_bytes += seq.small_pool.bytes() + seq.large_pool.bytes();
+   stats.directory_bytes += seq.large_entries.bytes() + seq.items.bytes() + seq.segs.bytes() + seq.slabs.bytes();
+   stats.payload_bytes += seq.postings.bytes() + seq.large_pool.bytes();
    stats.n_work_items += items.size();
-   stats.n_chunks += stage_recs.size();
+   stats.n_chunks += large_entries.size();
    SeqDev& d = seq.dev;
-   d.entries = seq.entries.ptr; d.stages = seq.stages.ptr; d.items = seq.items.ptr; d.segs = seq.segs.ptr; d.slabs = seq.slabs.ptr; d.slab_begin = seq.slab_begin.ptr;
-   d.small_pool = seq.small_pool.ptr; d.large_pool = seq.large_pool.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
+   d.postings = seq.postings.ptr; d.large_entries = seq.large_entries.ptr; d.items = seq.items.ptr; d.segs = seq.segs.ptr; d.slabs = seq.slabs.ptr; d.slab_begin = seq.slab_begin.ptr;
+   d.large_pool = seq.large_pool.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
    d.miss_row_off = seq.miss_row_off.ptr; d.miss_iv = seq.miss_iv.ptr; d.miss_row_base = seq.miss_row_base.ptr; d.miss_iv_base = seq.miss_iv_base.ptr;
    d.length = L; d.sigma = sigma; d.tile_positions = tp; d.n_tiles = seq.n_tiles; d.n_partitions = n_partitions;
-   d.n_items = seq.n_items; d.n_stages = seq.n_stages; d.n_slabs = n_slabs;
+   d.n_items = seq.n_items; d.n_slabs = n_slabs;
 }
 
 }  // namespace sb
