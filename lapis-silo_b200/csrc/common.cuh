@@ -91,7 +91,7 @@ struct WorkItem {            // one CTA of the Mutations scan: a weight-bounded 
    uint32_t slab;
    uint32_t post_begin, post_end;     // postings [begin, end), begin a multiple of 4
    uint32_t large_begin, large_end;   // large entries
-   uint32_t pad[2];
+   uint32_t partition, key0;          // of the slab (saves the scan a dependent load)
 };
 static_assert(sizeof(WorkItem) == 32, "WorkItem must be 32 bytes");
 

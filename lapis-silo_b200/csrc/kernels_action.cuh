@@ -67,10 +67,13 @@ __device__ __forceinline__ uint32_t filterRangeCount(const PartQuery& q, uint32_
 
 // Block -> work item: the items of every partition are contiguous (heaviest first); a query lists the
 // partial partitions as ranges. block_prefix[k] = first block of range k, item_first[k] = its first item.
+constexpr uint32_t K1_INLINE_RANGES = 32;
 struct K1Map {
-   const uint32_t* block_prefix;   // [n_ranges + 1]
+   const uint32_t* block_prefix;   // [n_ranges + 1]   (used when n_ranges > K1_INLINE_RANGES)
    const uint32_t* item_first;     // [n_ranges]
    uint32_t n_ranges;
+   uint32_t inline_prefix[K1_INLINE_RANGES + 1];   // the same in kernel-parameter (constant) memory
+   uint32_t inline_first[K1_INLINE_RANGES];
 };
 
 // One CTA per work item. Shared memory: [filter slab 32 KB][tile counts (tile_slots + 1 words)][mbarrier].
@@ -79,20 +82,26 @@ struct K1Map {
 __global__ void __launch_bounds__(K1_THREADS, 4)
 k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map map, uint32_t* __restrict__ counts, int full_mode) {
    extern __shared__ __align__(128) uint8_t k1_smem[];
-   uint32_t range = 0;
-   {  // few ranges (partial partitions): binary search in global memory (L2-resident)
+   uint32_t item_index;
+   if (map.n_ranges <= K1_INLINE_RANGES) {
+      uint32_t range = 0;
+#pragma unroll 1
+      for (uint32_t k = 1; k < map.n_ranges; ++k) if (map.inline_prefix[k] <= blockIdx.x) range = k;
+      item_index = map.inline_first[range] + (blockIdx.x - map.inline_prefix[range]);
+   } else {
       uint32_t lo = 0, hi = map.n_ranges;
       while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(map.block_prefix + mid) <= blockIdx.x) lo = mid; else hi = mid; }
-      range = lo;
+      item_index = __ldg(map.item_first + lo) + (blockIdx.x - __ldg(map.block_prefix + lo));
    }
-   const WorkItem item = s.items[__ldg(map.item_first + range) + (blockIdx.x - __ldg(map.block_prefix + range))];
-   const SlabRec slab = s.slabs[item.slab];
+   const WorkItem item = s.items[item_index];
+   const SlabRec slab{item.partition, item.key0};
    const PartQuery q = pq[slab.partition];
 
    uint32_t* filter_s = reinterpret_cast<uint32_t*>(k1_smem);
    uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES);
    const uint32_t T = s.tile_positions, tile_slots = T * s.sigma;
    uint64_t* bar = reinterpret_cast<uint64_t*>(tile_counts + ((tile_slots + 2) & ~1u));
+   uint32_t* next_chunk = reinterpret_cast<uint32_t*>(bar + 1);
 
    if (threadIdx.x == 0) {
       mbarInit(bar, 1);
@@ -102,19 +111,32 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    }
    for (uint32_t i = threadIdx.x; i <= tile_slots; i += K1_THREADS) tile_counts[i] = 0;
 
-   // posting loads do not depend on the filter: issue the first batch before waiting for it
+   // flags of this thread's flush position, fetched now so that the flush does not wait for them
+   const uint32_t flush_pos = item.tile * T + threadIdx.x;
+   int flush_del = -1, flush_flip = -1;
+   if (threadIdx.x < T && flush_pos < s.length) {
+      flush_del = s.deleted[size_t(slab.partition) * s.length + flush_pos];
+      flush_flip = s.flipped[size_t(slab.partition) * s.length + flush_pos];
+   }
+   // Postings are handed out to the warps in chunks of 128 x 16 bytes through a shared counter, so that a warp
+   // that is busy with a bitset simply takes fewer. The first chunk of every warp is fixed (chunk = warp id) and
+   // its loads are issued before waiting for the filter: they do not depend on it.
+   constexpr uint32_t CHUNK4 = 32 * K1_UNROLL;    // 128-bit words per chunk
+   constexpr uint32_t N_WARPS = K1_THREADS / 32;
+   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
    const uint4* post4 = reinterpret_cast<const uint4*>(s.postings + item.post_begin);
    const uint32_t n4 = (item.post_end - item.post_begin + 3u) >> 2;
+   const uint4 none = make_uint4(~0u, ~0u, ~0u, ~0u);
    uint4 v[K1_UNROLL];
-   uint32_t i0 = threadIdx.x;
+   uint32_t chunk = warp;
 #pragma unroll
-   for (int k = 0; k < K1_UNROLL; ++k) v[k] = i0 + k * K1_THREADS < n4 ? __ldg(post4 + i0 + k * K1_THREADS) : make_uint4(~0u, ~0u, ~0u, ~0u);
-   __syncthreads();      // counts zeroed, mbarrier initialised
+   for (int k = 0; k < K1_UNROLL; ++k) { const uint32_t i = chunk * CHUNK4 + k * 32 + lane; v[k] = i < n4 ? __ldg(post4 + i) : none; }
+   if (threadIdx.x == 0) *next_chunk = N_WARPS;
+   __syncthreads();      // counts zeroed, mbarrier and chunk counter initialised
    mbarWait(bar, 0);
 
-   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
-   // (1) large containers: one per warp at a time, 128-bit loads straight from the large pool
-   for (uint32_t j = item.large_begin + warp; j < item.large_end; j += K1_THREADS / 32) {
+   // (1) large containers: one per warp at a time, 8 x 128-bit loads per lane in flight for a bitset
+   for (uint32_t j = item.large_begin + warp; j < item.large_end; j += N_WARPS) {
       const LargeEntry w = s.large_entries[j];
       const uint4* src = s.large_pool + w.offset16;
       const uint32_t k_kind = w.kind(), k_local = w.keyLocal(), k_size = w.size;
@@ -154,33 +176,35 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    auto probe = [&](uint32_t p) {
       if ((filter_s[(p >> 5) & (SLAB_WORDS32 - 1)] >> (p & 31)) & 1u) atomicAdd(&tile_counts[p >> POSTING_ROW_BITS], 1u);
    };
-   for (; i0 < n4; i0 += K1_UNROLL * K1_THREADS) {
+   while (chunk * CHUNK4 < n4) {
+      uint32_t next = 0;
+      if (lane == 0) next = atomicAdd(next_chunk, 1u);
+      next = __shfl_sync(0xFFFFFFFFu, next, 0);
       uint4 nxt[K1_UNROLL];
-      const uint32_t i1 = i0 + K1_UNROLL * K1_THREADS;
 #pragma unroll
-      for (int k = 0; k < K1_UNROLL; ++k) nxt[k] = i1 + k * K1_THREADS < n4 ? __ldg(post4 + i1 + k * K1_THREADS) : make_uint4(~0u, ~0u, ~0u, ~0u);
+      for (int k = 0; k < K1_UNROLL; ++k) { const uint32_t i = next * CHUNK4 + k * 32 + lane; nxt[k] = i < n4 ? __ldg(post4 + i) : none; }
 #pragma unroll
       for (int k = 0; k < K1_UNROLL; ++k) {
-         if (i0 + k * K1_THREADS < n4) { probe(v[k].x); probe(v[k].y); probe(v[k].z); probe(v[k].w); }
+         if (chunk * CHUNK4 + k * 32 + lane < n4) { probe(v[k].x); probe(v[k].y); probe(v[k].z); probe(v[k].w); }
       }
 #pragma unroll
       for (int k = 0; k < K1_UNROLL; ++k) v[k] = nxt[k];
+      chunk = next;
    }
    __syncthreads();
    // (3) flush: thread = position of the tile; symbol rows of counts[sym][pos] get coalesced REDs
-   for (uint32_t pl = threadIdx.x; pl < T; pl += K1_THREADS) {
-      const uint32_t pos = item.tile * T + pl;
-      if (pos >= s.length) break;
-      const int del = s.deleted[size_t(slab.partition) * s.length + pos], flip = s.flipped[size_t(slab.partition) * s.length + pos];
+   static_assert(TILE_POSITIONS <= K1_THREADS, "one flush position per thread");
+   if (threadIdx.x < T && flush_pos < s.length) {
+      const uint32_t pl = threadIdx.x;
       int acc_deleted = 0;
       for (uint32_t sym = 0; sym < s.sigma; ++sym) {
          const int raw = int(tile_counts[sym * T + pl]);
-         if (raw == 0 || int(sym) == del) continue;
-         const int add_slot = int(sym) == flip ? -raw : raw;
-         atomicAdd(counts + size_t(sym) * s.length + pos, uint32_t(add_slot));
+         if (raw == 0 || int(sym) == flush_del) continue;
+         const int add_slot = int(sym) == flush_flip ? -raw : raw;
+         atomicAdd(counts + size_t(sym) * s.length + flush_pos, uint32_t(add_slot));
          acc_deleted += full_mode ? -raw : -add_slot;
       }
-      if (del >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(del) * s.length + pos, uint32_t(acc_deleted));
+      if (flush_del >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(flush_del) * s.length + flush_pos, uint32_t(acc_deleted));
    }
 }
 

@@ -134,7 +134,10 @@ struct RegisteredBitmap { uint32_t partition; uint32_t first_container, n_contai
 
 struct Column { uint32_t partition; int dtype; uint32_t n; void* device = nullptr; };
 
-constexpr uint64_t ITEM_WEIGHT_CAP = 256 * 1024;   // bytes of postings + large payload per Mutations work item
+inline uint64_t itemWeightCap() {   // bytes of postings + large payload per Mutations work item (SB_ITEM_CAP_KB: tuning)
+   const char* e = getenv("SB_ITEM_CAP_KB");
+   return (e && atoi(e) > 0 ? uint64_t(atoi(e)) : 128) * 1024;
+}
 
 // Packs the ingested stores of one sequence into the tiled device layout.
 inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>& stores, uint32_t n_partitions, sb_pool_stats& stats) {
@@ -170,6 +173,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    std::vector<Picked> picked;
    uint64_t hist[16] = {};   // SB_TRACE: array cardinalities 1,2,3,4,<=8,<=16,<=32,<=64,<=256,<=4096 | runs | bitsets
    const uint32_t filler = slots_per_tile << POSTING_ROW_BITS;
+   const uint64_t item_cap = itemWeightCap();
    for (uint32_t tile = 0; tile < seq.n_tiles; ++tile) {
       const uint32_t slot_end = (tile + 1) * slots_per_tile;
       for (uint32_t slab_id = 0; slab_id < n_slabs; ++slab_id) {
@@ -222,12 +226,12 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
          // cut the segment into weight-bounded work items: postings and large entries are split evenly
          const size_t n_post = postings.size() - post_begin, n_large = large_entries.size() - large_begin;
          const uint64_t weight = 4ull * n_post + large_bytes;
-         const uint32_t n_cuts = uint32_t(std::max<uint64_t>(1, (weight + ITEM_WEIGHT_CAP - 1) / ITEM_WEIGHT_CAP));
+         const uint32_t n_cuts = uint32_t(std::max<uint64_t>(1, (weight + item_cap - 1) / item_cap));
          for (uint32_t cut = 0; cut < n_cuts; ++cut) {
             auto postCut = [&](uint32_t c) { return c == n_cuts ? n_post : (n_post * c / n_cuts) & ~size_t(3); };
             const size_t pb = postCut(cut), pe = postCut(cut + 1), lb = n_large * cut / n_cuts, le = n_large * (cut + 1) / n_cuts;
             if (pb == pe && lb == le) continue;
-            items.push_back({tile, slab_id, uint32_t(post_begin + pb), uint32_t(post_begin + pe), uint32_t(large_begin + lb), uint32_t(large_begin + le), {0, 0}});
+            items.push_back({tile, slab_id, uint32_t(post_begin + pb), uint32_t(post_begin + pe), uint32_t(large_begin + lb), uint32_t(large_begin + le), p, key0});
             item_weight.push_back(4ull * (pe - pb) + (n_large ? large_bytes * (le - lb) / n_large : 0));
          }
          SB_REQUIRE(postings.size() < 0xFFFFFFF0ull, "more than 2^32 postings in one sequence");
