@@ -176,6 +176,10 @@ int sb_launch_count(const sb_db* db, uint64_t* launches);
 /* Bytes moved by cudaMemcpyAsync on the db's stream so far (plans / PartQuery up, cardinalities / tables down). */
 int sb_transfer_bytes(const sb_db* db, uint64_t* h2d, uint64_t* d2h);
 /* Accumulated CUDA-event time of k1_and_popcount since the last call with reset != 0, and its launch count. */
+/* By default independent kernels of a query overlap on a second stream (the row-wise leaves beside the container
+ * leaves; the missing-symbol kernel beside the container scan). enabled = 0 serialises them on one stream, which is
+ * how bench.py times the container scan alone for its roofline line. */
+int sb_set_overlap(sb_db* db, int enabled);
 int sb_k1_accumulated(sb_db* db, int reset, double* total_ms, uint64_t* launches);
 
 #ifdef __cplusplus

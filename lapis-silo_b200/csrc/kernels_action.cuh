@@ -65,15 +65,14 @@ __device__ __forceinline__ uint32_t filterRangeCount(const PartQuery& q, uint32_
    return r1 - r0 + __popcll(upto_b) - __popcll(below_a);
 }
 
-// Block -> work item: the items of every partition are contiguous (heaviest first); a query lists the
-// partial partitions as ranges. block_prefix[k] = first block of range k, item_first[k] = its first item.
-constexpr uint32_t K1_INLINE_RANGES = 32;
+// Block -> work item: a per-query list of the work items of the partial partitions, heaviest first over all
+// of them (longest-processing-time order: the block scheduler hands out CTAs in index order). The filter
+// pointers of the first K1_INLINE_PARTITIONS partitions travel in kernel-parameter (constant) memory so that
+// the bulk copy of the filter slab is one dependent load closer.
+constexpr uint32_t K1_INLINE_PARTITIONS = 64;
 struct K1Map {
-   const uint32_t* block_prefix;   // [n_ranges + 1]   (used when n_ranges > K1_INLINE_RANGES)
-   const uint32_t* item_first;     // [n_ranges]
-   uint32_t n_ranges;
-   uint32_t inline_prefix[K1_INLINE_RANGES + 1];   // the same in kernel-parameter (constant) memory
-   uint32_t inline_first[K1_INLINE_RANGES];
+   const uint32_t* item_list;                              // [grid]
+   const uint32_t* inline_filter[K1_INLINE_PARTITIONS];    // filter32 of partition p (p < K1_INLINE_PARTITIONS)
 };
 
 // One CTA per work item. Shared memory: [filter slab 32 KB][tile counts (tile_slots + 1 words)][mbarrier].
@@ -82,32 +81,21 @@ struct K1Map {
 __global__ void __launch_bounds__(K1_THREADS, 4)
 k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map map, uint32_t* __restrict__ counts, int full_mode) {
    extern __shared__ __align__(128) uint8_t k1_smem[];
-   uint32_t item_index;
-   if (map.n_ranges <= K1_INLINE_RANGES) {
-      uint32_t range = 0;
-#pragma unroll 1
-      for (uint32_t k = 1; k < map.n_ranges; ++k) if (map.inline_prefix[k] <= blockIdx.x) range = k;
-      item_index = map.inline_first[range] + (blockIdx.x - map.inline_prefix[range]);
-   } else {
-      uint32_t lo = 0, hi = map.n_ranges;
-      while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(map.block_prefix + mid) <= blockIdx.x) lo = mid; else hi = mid; }
-      item_index = __ldg(map.item_first + lo) + (blockIdx.x - __ldg(map.block_prefix + lo));
-   }
-   const WorkItem item = s.items[item_index];
+   const WorkItem item = s.items[__ldg(map.item_list + blockIdx.x)];
    const SlabRec slab{item.partition, item.key0};
-   const PartQuery q = pq[slab.partition];
+   const uint32_t* filter32 = slab.partition < K1_INLINE_PARTITIONS ? map.inline_filter[slab.partition] : pq[slab.partition].filter32;
 
    uint32_t* filter_s = reinterpret_cast<uint32_t*>(k1_smem);
    uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES);
    const uint32_t T = s.tile_positions, tile_slots = T * s.sigma;
    uint64_t* bar = reinterpret_cast<uint64_t*>(tile_counts + ((tile_slots + 2) & ~1u));
-   uint32_t* next_chunk = reinterpret_cast<uint32_t*>(bar + 1);
+   uint32_t* next_unit = reinterpret_cast<uint32_t*>(bar + 1);
 
    if (threadIdx.x == 0) {
       mbarInit(bar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       mbarExpectTx(bar, K1_FILTER_BYTES);
-      bulkLoad(filter_s, q.filter32 + size_t(slab.key0) * 2048u, K1_FILTER_BYTES, bar);
+      bulkLoad(filter_s, filter32 + size_t(slab.key0) * 2048u, K1_FILTER_BYTES, bar);
    }
    for (uint32_t i = threadIdx.x; i <= tile_slots; i += K1_THREADS) tile_counts[i] = 0;
 
@@ -118,33 +106,48 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
       flush_del = s.deleted[size_t(slab.partition) * s.length + flush_pos];
       flush_flip = s.flipped[size_t(slab.partition) * s.length + flush_pos];
    }
-   // Postings are handed out to the warps in chunks of 128 x 16 bytes through a shared counter, so that a warp
-   // that is busy with a bitset simply takes fewer. The first chunk of every warp is fixed (chunk = warp id) and
-   // its loads are issued before waiting for the filter: they do not depend on it.
+   // Work units of the item, handed out to the warps through a shared counter (a warp that is busy with a bitset
+   // simply takes fewer): first the large containers -- a bitset as two halves of 4 KB, anything else whole --
+   // then the postings in chunks of 128 x 16 bytes. The first unit of a warp is its warp id; the loads of a posting
+   // chunk are issued one unit ahead (and before waiting for the filter: they do not depend on it).
    constexpr uint32_t CHUNK4 = 32 * K1_UNROLL;    // 128-bit words per chunk
    constexpr uint32_t N_WARPS = K1_THREADS / 32;
    const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
    const uint4* post4 = reinterpret_cast<const uint4*>(s.postings + item.post_begin);
    const uint32_t n4 = (item.post_end - item.post_begin + 3u) >> 2;
+   const uint32_t n_large_units = 2u * (item.large_end - item.large_begin);
+   const uint32_t n_units = n_large_units + (n4 + CHUNK4 - 1) / CHUNK4;
    const uint4 none = make_uint4(~0u, ~0u, ~0u, ~0u);
    uint4 v[K1_UNROLL];
-   uint32_t chunk = warp;
+   auto loadChunk = [&](uint32_t unit, uint4 (&dst)[K1_UNROLL]) {
+      if (unit < n_large_units || unit >= n_units) return;
+      const uint32_t base = (unit - n_large_units) * CHUNK4 + lane;
 #pragma unroll
-   for (int k = 0; k < K1_UNROLL; ++k) { const uint32_t i = chunk * CHUNK4 + k * 32 + lane; v[k] = i < n4 ? __ldg(post4 + i) : none; }
-   if (threadIdx.x == 0) *next_chunk = N_WARPS;
-   __syncthreads();      // counts zeroed, mbarrier and chunk counter initialised
+      for (int k = 0; k < K1_UNROLL; ++k) dst[k] = base + k * 32 < n4 ? __ldg(post4 + base + k * 32) : none;
+   };
+   auto grab = [&]() {
+      uint32_t next = 0;
+      if (lane == 0) next = atomicAdd(next_unit, 1u);
+      return __shfl_sync(0xFFFFFFFFu, next, 0);
+   };
+   uint32_t unit = warp;
+   loadChunk(unit, v);
+   if (threadIdx.x == 0) *next_unit = N_WARPS;
+   __syncthreads();      // counts zeroed, mbarrier and unit counter initialised
    mbarWait(bar, 0);
 
-   // (1) large containers: one per warp at a time, 8 x 128-bit loads per lane in flight for a bitset
-   for (uint32_t j = item.large_begin + warp; j < item.large_end; j += N_WARPS) {
-      const LargeEntry w = s.large_entries[j];
-      const uint4* src = s.large_pool + w.offset16;
-      const uint32_t k_kind = w.kind(), k_local = w.keyLocal(), k_size = w.size;
-      int c2 = 0;
-      if (k_kind == KIND_BITSET) {
-         const uint4* fk = reinterpret_cast<const uint4*>(filter_s) + k_local * 512u;
-#pragma unroll
-         for (uint32_t half = 0; half < 2; ++half) {
+   auto probe = [&](uint32_t p) {
+      if ((filter_s[(p >> 5) & (SLAB_WORDS32 - 1)] >> (p & 31)) & 1u) atomicAdd(&tile_counts[p >> POSTING_ROW_BITS], 1u);
+   };
+   while (unit < n_units) {
+      if (unit < n_large_units) {
+         const LargeEntry w = s.large_entries[item.large_begin + (unit >> 1)];
+         const uint32_t half = unit & 1u;
+         const uint4* src = s.large_pool + w.offset16;
+         const uint32_t k_kind = w.kind(), k_local = w.keyLocal(), k_size = w.size;
+         int c2 = 0;
+         if (k_kind == KIND_BITSET) {
+            const uint4* fk = reinterpret_cast<const uint4*>(filter_s) + k_local * 512u;
             uint4 x[8];
 #pragma unroll
             for (uint32_t t = 0; t < 8; ++t) x[t] = __ldg(src + (half * 8 + t) * 32 + lane);
@@ -153,43 +156,39 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
                const uint4 y = fk[(half * 8 + t) * 32 + lane];
                c2 += __popc(x[t].x & y.x) + __popc(x[t].y & y.y) + __popc(x[t].z & y.z) + __popc(x[t].w & y.w);
             }
-         }
-      } else if (k_kind == KIND_ARRAY) {
-         const uint32_t* fk = filter_s + k_local * 2048u;
-         for (uint32_t i = lane; i * 8 < k_size; i += 32) {
-            const uint4 x = __ldg(src + i);
-            const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
+         } else if (half == 0 && k_kind == KIND_ARRAY) {
+            const uint32_t* fk = filter_s + k_local * 2048u;
+            for (uint32_t i = lane; i * 8 < k_size; i += 32) {
+               const uint4 x = __ldg(src + i);
+               const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-            for (uint32_t t = 0; t < 8; ++t) {
-               const uint32_t val = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
-               if (i * 8 + t < k_size) c2 += (fk[val >> 5] >> (val & 31)) & 1u;
+               for (uint32_t t = 0; t < 8; ++t) {
+                  const uint32_t val = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
+                  if (i * 8 + t < k_size) c2 += (fk[val >> 5] >> (val & 31)) & 1u;
+               }
             }
+         } else if (half == 0) {   // long run container: two rank lookups per run
+            const uint16_t* runs = reinterpret_cast<const uint16_t*>(src);
+            const PartQuery q = pq[slab.partition];
+            for (uint32_t i = lane; i < k_size; i += 32) { const uint32_t start = __ldg(runs + 2 * i), len1 = __ldg(runs + 2 * i + 1); c2 += int(filterRangeCount(q, slab.key0 + k_local, start, start + len1)); }
          }
-      } else {   // long run container: two rank lookups per run
-         const uint16_t* runs = reinterpret_cast<const uint16_t*>(src);
-         for (uint32_t i = lane; i < k_size; i += 32) { const uint32_t start = __ldg(runs + 2 * i), len1 = __ldg(runs + 2 * i + 1); c2 += int(filterRangeCount(q, slab.key0 + k_local, start, start + len1)); }
+         c2 = warpSum(c2);
+         if (lane == 0 && c2 != 0) atomicAdd(&tile_counts[w.slot()], uint32_t(c2));
+         unit = grab();
+         loadChunk(unit, v);
+      } else {
+         const uint32_t next = grab();
+         uint4 nx[K1_UNROLL];
+         loadChunk(next, nx);
+         const uint32_t base = (unit - n_large_units) * CHUNK4 + lane;
+#pragma unroll
+         for (int k = 0; k < K1_UNROLL; ++k) {
+            if (base + k * 32 < n4) { probe(v[k].x); probe(v[k].y); probe(v[k].z); probe(v[k].w); }
+         }
+#pragma unroll
+         for (int k = 0; k < K1_UNROLL; ++k) v[k] = nx[k];
+         unit = next;
       }
-      c2 = warpSum(c2);
-      if (lane == 0 && c2 != 0) atomicAdd(&tile_counts[w.slot()], uint32_t(c2));
-   }
-   // (2) postings: probe the shared-memory filter, count hits per slot
-   auto probe = [&](uint32_t p) {
-      if ((filter_s[(p >> 5) & (SLAB_WORDS32 - 1)] >> (p & 31)) & 1u) atomicAdd(&tile_counts[p >> POSTING_ROW_BITS], 1u);
-   };
-   while (chunk * CHUNK4 < n4) {
-      uint32_t next = 0;
-      if (lane == 0) next = atomicAdd(next_chunk, 1u);
-      next = __shfl_sync(0xFFFFFFFFu, next, 0);
-      uint4 nxt[K1_UNROLL];
-#pragma unroll
-      for (int k = 0; k < K1_UNROLL; ++k) { const uint32_t i = next * CHUNK4 + k * 32 + lane; nxt[k] = i < n4 ? __ldg(post4 + i) : none; }
-#pragma unroll
-      for (int k = 0; k < K1_UNROLL; ++k) {
-         if (chunk * CHUNK4 + k * 32 + lane < n4) { probe(v[k].x); probe(v[k].y); probe(v[k].z); probe(v[k].w); }
-      }
-#pragma unroll
-      for (int k = 0; k < K1_UNROLL; ++k) v[k] = nxt[k];
-      chunk = next;
    }
    __syncthreads();
    // (3) flush: thread = position of the tile; symbol rows of counts[sym][pos] get coalesced REDs

@@ -29,7 +29,9 @@ struct PlanDesc {
    uint64_t rank_local_off;       // uint32 offset
    uint64_t rank_block_off;       // uint32 offset
    uint64_t* cardinality;         // device counter
+   uint32_t leaf_off, n_leaves;   // the plan's slice of the leaf table (P_LEAF operands index it)
 };
+struct LeafRef { uint64_t off; uint32_t words; uint32_t pad; };   // dense scratch bitset of a leaf: word offset, length
 
 struct PosLeafJob { uint32_t seq, partition, slot, slab; uint64_t dst_off; uint32_t dst_words, pad2; };   // one per (leaf, slab)
 struct RegContainer { uint64_t pay_off; uint32_t size; uint16_t key; uint8_t kind; uint8_t pad; };  // size: array card / #runs
@@ -57,7 +59,25 @@ __device__ __forceinline__ void scatterContainer(uint64_t* dst, uint32_t n_words
                                                  const uint16_t* pay, const uint4* bitset, uint32_t lane) {
    const uint32_t base = key << 16;
    if (kind == KIND_ARRAY) {
-      for (uint32_t i = lane; i < size; i += 32) setBit(dst, n_words, base | __ldg(pay + i));
+      if ((reinterpret_cast<uintptr_t>(pay) & 15u) == 0) {   // 8 values per load, 4 loads per lane in flight
+         const uint4* pay4 = reinterpret_cast<const uint4*>(pay);
+         const uint32_t n4 = (size + 7) / 8;
+         for (uint32_t i0 = lane; i0 < n4; i0 += 128) {
+            uint4 x[4];
+#pragma unroll
+            for (uint32_t k = 0; k < 4; ++k) x[k] = i0 + k * 32 < n4 ? __ldg(pay4 + i0 + k * 32) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (uint32_t k = 0; k < 4; ++k) {
+               const uint32_t wv[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
+#pragma unroll
+               for (uint32_t t = 0; t < 8; ++t) {
+                  if ((i0 + k * 32) * 8 + t < size) setBit(dst, n_words, base | ((wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu));
+               }
+            }
+         }
+      } else {
+         for (uint32_t i = lane; i < size; i += 32) setBit(dst, n_words, base | __ldg(pay + i));
+      }
    } else if (kind == KIND_RUN) {
       for (uint32_t r = 0; r < size; ++r) {
          const uint32_t start = __ldg(pay + 2 * r), len1 = __ldg(pay + 2 * r + 1);
@@ -67,8 +87,14 @@ __device__ __forceinline__ void scatterContainer(uint64_t* dst, uint32_t n_words
       // a bitmap has one container per key and every leaf owns its scratch region: plain 128-bit copy
       if ((key + 1u) * 1024u <= n_words) {
          uint4* out = reinterpret_cast<uint4*>(dst + size_t(key) * 1024u);
-#pragma unroll 4
-         for (uint32_t i = lane; i < 512; i += 32) out[i] = __ldg(bitset + i);
+#pragma unroll
+         for (uint32_t half = 0; half < 2; ++half) {
+            uint4 x[8];
+#pragma unroll
+            for (uint32_t t = 0; t < 8; ++t) x[t] = __ldg(bitset + (half * 8 + t) * 32 + lane);
+#pragma unroll
+            for (uint32_t t = 0; t < 8; ++t) out[(half * 8 + t) * 32 + lane] = x[t];
+         }
       } else {
          const uint64_t* src = reinterpret_cast<const uint64_t*>(bitset);
          for (uint32_t i = lane; i < 1024; i += 32) {
@@ -91,17 +117,29 @@ __global__ void leaf_position_bitmap(const SeqDev* __restrict__ seqs, const PosL
    const SegRec seg = s.segs[size_t(tile) * s.n_slabs + job.slab];
    const SegRec next = s.segs[size_t(tile) * s.n_slabs + job.slab + 1];
    const uint32_t key0 = s.slabs[job.slab].key0;
-   {  // postings: lower bound of slot2 << 18, then the run of equal slots, lanes strided
+   {  // postings: warp-wide 32-ary lower bound of slot2 << 18 (3 dependent loads for a 32 K segment), then the run of equal slots
       const uint32_t target = slot2 << POSTING_ROW_BITS;
-      uint32_t lo = seg.post_start, hi = next.post_start;
-      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(s.postings + mid) < target) lo = mid + 1; else hi = mid; }
+      uint32_t lo = seg.post_start, hi = next.post_start;   // answer in [lo, hi]
+      while (hi - lo > 32) {
+         const uint32_t step = (hi - lo + 31) / 32;           // probes at lo + k*step - 1 ... cover the range
+         const uint32_t at = min(lo + (lane + 1) * step, hi) - 1;
+         const bool below = __ldg(s.postings + at) < target;   // monotone in lane
+         const uint32_t n_below = __popc(__ballot_sync(0xFFFFFFFFu, below));
+         const uint32_t new_lo = n_below == 0 ? lo : min(lo + n_below * step, hi);
+         const uint32_t new_hi = n_below == 32 ? hi : min(lo + (n_below + 1) * step, hi) - 1;
+         lo = new_lo; hi = max(new_hi, new_lo);
+      }
+      {
+         const bool below = lo + lane < hi && __ldg(s.postings + lo + lane) < target;
+         lo += __popc(__ballot_sync(0xFFFFFFFFu, below));
+      }
       for (uint32_t e = lo + lane; e < next.post_start; e += 32) {
          const uint32_t p = __ldg(s.postings + e);
          if ((p >> POSTING_ROW_BITS) != slot2) break;
          setBit(dst, job.dst_words, (key0 << 16) + (p & POSTING_ROW_MASK));
       }
    }
-   {  // large containers of the slot
+   {  // large containers of the slot (few per segment: plain binary search)
       uint32_t lo = seg.large_start, hi = next.large_start;
       while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (s.large_entries[mid].slot() < slot2) lo = mid + 1; else hi = mid; }
       for (uint32_t e = lo; e < next.large_start; ++e) {
@@ -124,26 +162,49 @@ __global__ void leaf_registered(const RegContainer* __restrict__ containers, con
    scatterContainer(scratch + job.dst_off, job.dst_words, c.key, c.kind, c.size, pay, reinterpret_cast<const uint4*>(pay), lane);
 }
 
-// thread per row: does the row's missing-symbol bitmap contain `value`?  grid.y = job
-__global__ void leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict__ jobs, uint64_t* __restrict__ scratch) {
+// does the row's missing-symbol bitmap contain `value`?  grid.y = job. A thread owns BSEL_ROWS rows (256 apart, so that
+// every load stays coalesced) and walks their binary searches in lockstep: the kernel is a chain of dependent loads
+// per row, and four independent chains per thread hide four times as much of it.
+constexpr uint32_t BSEL_ROWS = 4;
+__global__ void __launch_bounds__(256)
+leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict__ jobs, uint64_t* __restrict__ scratch) {
    const BselJob job = jobs[blockIdx.y];
-   const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+   const uint32_t row0 = blockIdx.x * (256 * BSEL_ROWS) + threadIdx.x;
+   if (blockIdx.x * (256 * BSEL_ROWS) >= job.n_rows) return;
    const SeqDev& s = seqs[job.seq];
-   bool hit = false;
-   if (row < job.n_rows) {
-      const uint32_t* row_off = s.miss_row_off + s.miss_row_base[job.partition];
-      const uint2* iv = s.miss_iv + s.miss_iv_base[job.partition];
-      uint32_t lo = __ldg(row_off + row), hi = __ldg(row_off + row + 1);
-      bool contains = false;
-      while (lo < hi) {   // intervals are sorted and disjoint
-         const uint32_t mid = (lo + hi) >> 1;
-         const uint2 r = __ldg(iv + mid);
-         if (job.value < r.x) hi = mid; else if (job.value >= r.y) lo = mid + 1; else { contains = true; break; }
-      }
-      hit = contains == (job.contains != 0);
+   const uint32_t* row_off = s.miss_row_off + s.miss_row_base[job.partition];
+   const uint2* iv = s.miss_iv + s.miss_iv_base[job.partition];
+   uint32_t lo[BSEL_ROWS], hi[BSEL_ROWS];
+   bool contains[BSEL_ROWS];
+#pragma unroll
+   for (uint32_t k = 0; k < BSEL_ROWS; ++k) {
+      const uint32_t row = row0 + k * 256;
+      lo[k] = hi[k] = 0;
+      contains[k] = false;
+      if (row < job.n_rows) { lo[k] = __ldg(row_off + row); hi[k] = __ldg(row_off + row + 1); }
    }
-   const uint32_t bits = __ballot_sync(0xFFFFFFFFu, hit);
-   if (laneId() == 0 && bits) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[row >> 5] = bits;
+   bool any = true;
+   while (any) {   // intervals are sorted and disjoint
+      any = false;
+      uint2 r[BSEL_ROWS];
+      uint32_t mid[BSEL_ROWS];
+#pragma unroll
+      for (uint32_t k = 0; k < BSEL_ROWS; ++k) { mid[k] = (lo[k] + hi[k]) >> 1; if (lo[k] < hi[k]) r[k] = __ldg(iv + mid[k]); }
+#pragma unroll
+      for (uint32_t k = 0; k < BSEL_ROWS; ++k) {
+         if (lo[k] < hi[k]) {
+            if (job.value < r[k].x) hi[k] = mid[k]; else if (job.value >= r[k].y) lo[k] = mid[k] + 1; else { contains[k] = true; hi[k] = lo[k]; }
+            any |= lo[k] < hi[k];
+         }
+      }
+   }
+#pragma unroll
+   for (uint32_t k = 0; k < BSEL_ROWS; ++k) {
+      const uint32_t row = row0 + k * 256;
+      const bool hit = row < job.n_rows && contains[k] == (job.contains != 0);
+      const uint32_t bits = __ballot_sync(0xFFFFFFFFu, hit);
+      if (laneId() == 0 && bits) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[row >> 5] = bits;
+   }
 }
 
 template <typename T>
@@ -183,76 +244,119 @@ __device__ __forceinline__ uint64_t rangeMask(uint32_t w, uint32_t a, uint32_t b
    return m;
 }
 
-// grid: (ceil(max n_words_padded / 256), n_plans); each thread owns one 64-bit word of one plan
+// grid: (ceil(max n_words_padded / 256), n_plans); each thread owns one 64-bit word of one plan.
+// The interpreter is a serial fetch-decode chain per thread, so memory latency is taken out of it: the program and
+// the plan's leaf table are staged in shared memory, and the thread's words of the leaves -- consumed strictly in
+// program order -- are fetched eight at a time into a register window (eight independent loads in flight).
+// The top of the evaluation stack lives in a register; deeper entries in local memory.
+constexpr uint32_t INTERP_PROG_SMEM = 2048;   // program words staged in shared memory (longer programs are read from global)
+constexpr uint32_t INTERP_LEAF_SMEM = 128;    // leaf table entries staged in shared memory
 __global__ void __launch_bounds__(INTERP_THREADS)
-interpret_plans(const PlanDesc* __restrict__ plans, const uint32_t* __restrict__ programs, const uint64_t* __restrict__ scratch,
-                uint64_t* __restrict__ out, uint32_t* __restrict__ ranks) {
+interpret_plans(const PlanDesc* __restrict__ plans, const uint32_t* __restrict__ programs, const LeafRef* __restrict__ leaf_table,
+                const uint64_t* __restrict__ scratch, uint64_t* __restrict__ out, uint32_t* __restrict__ ranks) {
+   __shared__ uint32_t prog_s[INTERP_PROG_SMEM];
+   __shared__ LeafRef leaf_s[INTERP_LEAF_SMEM];
+   __shared__ int warp_sums[INTERP_THREADS / 32];
    const PlanDesc plan = plans[blockIdx.y];
    const uint32_t w = blockIdx.x * INTERP_THREADS + threadIdx.x;
    if (blockIdx.x * INTERP_THREADS >= plan.n_words_padded) return;
    uint64_t result = 0;
-   if (w < plan.n_words) {
+   if (blockIdx.x * INTERP_THREADS < plan.n_words) {
+      const uint32_t* prog = programs + plan.prog_off;
+      const LeafRef* leaves = leaf_table + plan.leaf_off;
+      if (plan.prog_len <= INTERP_PROG_SMEM) {
+         for (uint32_t i = threadIdx.x; i < plan.prog_len; i += INTERP_THREADS) prog_s[i] = prog[i];
+         prog = prog_s;
+      }
+      if (plan.n_leaves <= INTERP_LEAF_SMEM) {
+         for (uint32_t i = threadIdx.x; i < plan.n_leaves; i += INTERP_THREADS) leaf_s[i] = leaves[i];
+         leaves = leaf_s;
+      }
+      __syncthreads();
+      uint64_t win[8];      // words of leaves [8 * batch, 8 * batch + 8)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) win[k] = 0;
+      uint32_t next_leaf = 0;
       uint64_t stack[INTERP_STACK];
+      uint64_t tos = 0;   // top of stack; stack[0 .. sp-2] below it
       int sp = 0;
-      const uint32_t* pc = programs + plan.prog_off;
+      const uint32_t* pc = prog;
       const uint32_t* end = pc + plan.prog_len;
+#define SB_PUSH(value) do { if (sp > 0) stack[sp - 1] = tos; tos = (value); ++sp; } while (0)
       while (pc < end) {
          const uint32_t op = *pc++;
          switch (op) {
-            case P_ZERO: stack[sp++] = 0; break;
+            case P_ZERO: SB_PUSH(0ULL); break;
             case P_RANGES: {
                const uint32_t n = *pc++;
                uint64_t m = 0;
                for (uint32_t k = 0; k < n; ++k) { m |= rangeMask(w, pc[0], pc[1]); pc += 2; }
-               stack[sp++] = m;
+               SB_PUSH(m);
                break;
             }
-            case P_LEAF: {
-               const uint64_t off = uint64_t(pc[0]) | (uint64_t(pc[1]) << 32);
-               const uint32_t words = pc[2];
-               pc += 3;
-               stack[sp++] = w < words ? __ldg(scratch + off + w) : 0ULL;
+            case P_LEAF: {   // operand = index in the leaf table = number of leaves consumed so far
+               ++pc;
+               const uint32_t k = next_leaf & 7u;
+               if (k == 0) {
+#pragma unroll
+                  for (uint32_t q = 0; q < 8; ++q) {
+                     win[q] = 0;
+                     if (next_leaf + q < plan.n_leaves) { const LeafRef r = leaves[next_leaf + q]; if (w < r.words) win[q] = __ldg(scratch + r.off + w); }
+                  }
+               }
+               uint64_t v;
+               switch (k) {
+                  case 0: v = win[0]; break; case 1: v = win[1]; break; case 2: v = win[2]; break; case 3: v = win[3]; break;
+                  case 4: v = win[4]; break; case 5: v = win[5]; break; case 6: v = win[6]; break; default: v = win[7]; break;
+               }
+               ++next_leaf;
+               SB_PUSH(v);
                break;
             }
-            case P_NOT: { const uint32_t rc = *pc++; stack[sp - 1] ^= rangeMask(w, 0, rc); break; }   // flip(0, row_count)
-            case P_AND: --sp; stack[sp - 1] &= stack[sp]; break;
-            case P_OR: --sp; stack[sp - 1] |= stack[sp]; break;
-            case P_ANDNOT: --sp; stack[sp - 1] &= ~stack[sp]; break;
-            case P_THR_INIT: { const uint32_t d = *pc++; for (uint32_t j = 0; j < d; ++j) stack[sp++] = 0; break; }
+            case P_NOT: { const uint32_t rc = *pc++; tos ^= rangeMask(w, 0, rc); break; }   // flip(0, row_count)
+            case P_AND: --sp; tos = stack[sp - 1] & tos; break;
+            case P_OR: --sp; tos = stack[sp - 1] | tos; break;
+            case P_ANDNOT: --sp; tos = stack[sp - 1] & ~tos; break;
+            case P_THR_INIT: { const uint32_t d = *pc++; for (uint32_t j = 0; j < d; ++j) SB_PUSH(0ULL); break; }
             case P_THR_ADD: {   // threshold.cpp:92-129, one child; T[j] = rows matching >= j+1 children so far
                const int d = int(pc[0]), i = int(pc[1]), n = int(pc[2]), k = int(pc[3]);
                const uint32_t negated = pc[4], rc = pc[5];
                pc += 6;
-               const uint64_t c = stack[--sp];
-               uint64_t* t = stack + sp - d;
+               const uint64_t c = tos;
+               --sp;
+               uint64_t* t = stack + sp - d;     // the d planes are all in memory while a child is evaluated
                const int lo = max(0, n - k + i - 1);
                for (int j = min(d - 1, i); j > lo; --j) t[j] |= negated ? (t[j - 1] & ~c) : (t[j - 1] & c);
                if (k - i > n - 1) t[0] |= negated ? (c ^ rangeMask(w, 0, rc)) : c;
+               tos = t[d - 1];
                break;
             }
             case P_THR_FIN: {
                const int d = int(pc[0]), n = int(pc[1]);
                const uint32_t exact = pc[2];
                pc += 3;
+               stack[sp - 1] = tos;
                const uint64_t* t = stack + sp - d;
                const uint64_t r = exact ? (t[n - 1] & ~t[n]) : t[d - 1];
                sp -= d;
-               stack[sp++] = r;
+               ++sp;
+               tos = r;
                break;
             }
             default: pc = end; break;
          }
       }
-      result = stack[0];
+#undef SB_PUSH
+      if (w < plan.n_words) result = tos;
    }
    out[plan.out_off + w] = result;
    // rank tables: exclusive popcount prefix inside this 256-word block, and the block total
-   __shared__ int warp_sums[INTERP_THREADS / 32];
    const int pc_w = __popcll(result);
    const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
    int incl = pc_w;
 #pragma unroll
    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
+   __syncthreads();
    if (lane == 31) warp_sums[warp] = incl;
    __syncthreads();
    int before = 0, total = 0;

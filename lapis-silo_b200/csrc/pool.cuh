@@ -118,6 +118,7 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<uint4> large_pool;
    std::vector<uint32_t> h_slab_begin;    // [P + 1]
    std::vector<uint32_t> h_item_begin;    // [P + 1] work items of each partition (items are ordered by partition, then weight)
+   std::vector<uint32_t> h_item_weight;   // [n_items] bytes of postings + large payload
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
@@ -247,6 +248,8 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
       std::vector<WorkItem> sorted(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) sorted[k] = items[order[k]];
       items.swap(sorted);
+      seq.h_item_weight.resize(items.size());
+      for (uint32_t k = 0; k < order.size(); ++k) seq.h_item_weight[k] = uint32_t(std::min<uint64_t>(item_weight[order[k]], 0xFFFFFFFFull));
       seq.h_item_begin.assign(n_partitions + 1, 0);
       for (const WorkItem& it : items) seq.h_item_begin[slabs[it.slab].partition + 1]++;
       for (uint32_t p = 0; p < n_partitions; ++p) seq.h_item_begin[p + 1] += seq.h_item_begin[p];

@@ -63,11 +63,12 @@ struct sb_db {
    uint32_t n_partitions = 0;
    bool finalized = false;
    std::mutex mutex;
-   cudaStream_t stream = nullptr;
+   cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: kernels independent of the main chain (fork / join through events)
+   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
    cudaEvent_t ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr, ev_timer_begin = nullptr, ev_timer_end = nullptr;
    uint64_t launch_count = 0, k1_launches = 0, h2d_bytes = 0, d2h_bytes = 0;
    double k1_total_ms = 0;
-   bool timing_valid = false, k1_ran = false;
+   bool timing_valid = false, k1_ran = false, overlap = true;
    uint32_t last_launches = 0;
 
    std::vector<std::unique_ptr<HostStore>> stores;
@@ -83,13 +84,15 @@ struct sb_db {
    std::vector<Column> columns;
 
    PinnedBuffer staging, counts_host;
-   GrowDevice blob, scratch, action_scratch;
+   GrowDevice blob, scratch, action_scratch, table_scratch;
    sb_pool_stats stats{};
 
    ~sb_db() {
       cudaSetDevice(device);
       for (auto& c : columns) if (c.device) cudaFree(c.device);
       if (ev_begin) { cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); cudaEventDestroy(ev_timer_begin); cudaEventDestroy(ev_timer_end); }
+      if (ev_fork) { cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); }
+      if (stream2) cudaStreamDestroy(stream2);
       if (stream) cudaStreamDestroy(stream);
    }
 };
@@ -119,6 +122,9 @@ int sb_db_create(int device, uint32_t n_partitions, sb_db** out) {
       SB_CUDA(cudaDeviceGetAttribute(&db->sm_count, cudaDevAttrMultiProcessorCount, device));
       db->n_partitions = n_partitions;
       SB_CUDA(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
+      SB_CUDA(cudaStreamCreateWithFlags(&db->stream2, cudaStreamNonBlocking));
+      SB_CUDA(cudaEventCreateWithFlags(&db->ev_fork, cudaEventDisableTiming));
+      SB_CUDA(cudaEventCreateWithFlags(&db->ev_join, cudaEventDisableTiming));
       {  // keep freed result slabs in the stream-ordered pool: a query must not pay for cudaMalloc
          cudaMemPool_t pool;
          SB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));

@@ -58,7 +58,7 @@ void* silo_engine_handle(void* engine) { return static_cast<DeviceDatabase*>(eng
 // QueryEngine::executeQuery (query_engine.cpp:30-68) -> {"queryResult": [...]}
 char* silo_engine_execute(void* engine, const char* query_json) {
    char* out = nullptr;
-   capi::guarded([&] { out = capi::dupString(toJson(static_cast<DeviceDatabase*>(engine)->executeQuery(query_json)).dump()); });
+   capi::guarded([&] { out = capi::dupString(dumpJson(static_cast<DeviceDatabase*>(engine)->executeQuery(query_json))); });
    return out;
 }
 
@@ -174,7 +174,7 @@ char* silo_query_finish(void* state_, uint32_t reduced_count) {
          }
          return r;
       });
-      out = capi::dupString(toJson(result).dump());
+      out = capi::dupString(dumpJson(result));
    });
    return out;
 }
@@ -194,7 +194,7 @@ char* silo_rows_from_table(const void* db_, const char* query_json, const char* 
          addMutationsToOutput(sequence_name, alphabetById(alphabet_id), reference, counts, query.action.min_proportion, r.query_result);
          return r;
       });
-      out = capi::dupString(toJson(result).dump());
+      out = capi::dupString(dumpJson(result));
    });
    return out;
 }

@@ -3,6 +3,7 @@
 // from-scratch, dependency-free equivalent that keeps the number-kind distinction the
 // reference's validation relies on (is_number_unsigned / is_number_integer / is_number_float).
 #pragma once
+#include <charconv>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -97,18 +98,7 @@ class Value {
          case BOOL: out += b ? "true" : "false"; break;
          case UINT: out += std::to_string(u); break;
          case INT: out += std::to_string(i); break;
-         case FLOAT: {
-            if (std::isnan(d) || std::isinf(d)) { out += "null"; break; }
-            char buf[40];
-            // shortest round-trip form
-            for (int prec = 15; prec <= 17; ++prec) {
-               snprintf(buf, sizeof buf, "%.*g", prec, d);
-               if (strtod(buf, nullptr) == d) break;
-            }
-            out += buf;
-            if (!strpbrk(buf, ".eE")) out += ".0";
-            break;
-         }
+         case FLOAT: writeDouble(out, d); break;
          case STRING: writeString(out, s); break;
          case ARRAY: {
             out += '[';
@@ -128,6 +118,20 @@ class Value {
             break;
          }
       }
+   }
+   // Shortest form that parses back to the same double, written like printf("%.{n}g"): n = the number of significant
+   // digits of the shortest round-trip representation (std::to_chars) but at least 15, i.e. the first of %.15g, %.16g, %.17g that round-trips.
+   static void writeDouble(std::string& out, double d) {
+      if (std::isnan(d) || std::isinf(d)) { out += "null"; return; }
+      char tmp[48], buf[48];
+      const auto shortest = std::to_chars(tmp, tmp + sizeof tmp, d, std::chars_format::scientific);
+      int digits = 0;
+      for (const char* c = tmp; c < shortest.ptr && *c != 'e'; ++c) digits += *c >= '0' && *c <= '9';
+      const auto r = std::to_chars(buf, buf + sizeof buf, d, std::chars_format::general, std::max(digits, 15));
+      out.append(buf, r.ptr);
+      bool integral = true;
+      for (const char* c = buf; c < r.ptr; ++c) if (*c == '.' || *c == 'e' || *c == 'E') { integral = false; break; }
+      if (integral) out += ".0";
    }
    static void writeString(std::string& out, const std::string& str) {
       out += '"';

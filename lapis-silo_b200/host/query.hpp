@@ -33,6 +33,34 @@ inline json::Value toJson(const QueryResult& result) {  // query_result.cpp:10-2
    return out;
 }
 
+// The same text as toJson(result).dump(), written straight into the string (no intermediate tree): this is the
+// response body of every query.
+inline std::string dumpJson(const QueryResult& result) {
+   std::string out;
+   out.reserve(64 + result.query_result.size() * 96);
+   out += "{\"queryResult\":[";
+   bool first_entry = true;
+   for (const auto& entry : result.query_result) {
+      if (!first_entry) out += ',';
+      first_entry = false;
+      out += '{';
+      bool first_field = true;
+      for (const auto& [field, value] : entry.fields) {
+         if (!first_field) out += ',';
+         first_field = false;
+         json::Value::writeString(out, field);
+         out += ':';
+         if (!value) out += "null";
+         else if (std::holds_alternative<std::string>(*value)) json::Value::writeString(out, std::get<std::string>(*value));
+         else if (std::holds_alternative<int32_t>(*value)) out += std::to_string(std::get<int32_t>(*value));
+         else json::Value::writeDouble(out, std::get<double>(*value));
+      }
+      out += '}';
+   }
+   out += "]}";
+   return out;
+}
+
 struct OrderByField { std::string name; bool ascending; };
 
 enum class ActionType { AGGREGATED, MUTATIONS, AA_MUTATIONS };

@@ -282,6 +282,12 @@ def k1_accumulated(engine, reset=False):
     return ms.value, n.value
 
 
+def set_overlap(engine, enabled):
+    lib = _sb()
+    lib.sb_set_overlap.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    _sb_check(lib.sb_set_overlap(engine.sb, int(enabled)))
+
+
 def pool_stats(engine):
     st = PoolStats()
     _sb_check(_sb().sb_pool_get_stats(engine.sb, ctypes.byref(st)))
