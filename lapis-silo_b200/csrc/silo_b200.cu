@@ -3,6 +3,7 @@
 // filter evaluation (replaces Operator::evaluate), api_action.inc the Mutations / Aggregated actions.
 #include "common.cuh"
 #include "kernels_action.cuh"
+#include "kernels_scan.cuh"
 #include "kernels_filter.cuh"
 #include "pool.cuh"
 
@@ -69,6 +70,9 @@ struct sb_db {
    uint64_t launch_count = 0, k1_launches = 0, h2d_bytes = 0, d2h_bytes = 0;
    double k1_total_ms = 0;
    bool timing_valid = false, k1_ran = false, overlap = true;
+   uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of the scan (0 = one per SM)
+   bool classic_k1 = getenv("SB_K1_SCAN") == nullptr;   // default: one CTA per work item (k1_and_popcount). SB_K1_SCAN=1: the experimental persistent
+                                                        // producer/consumer pipeline (kernels_scan.cuh) -- bit-exact, but 2.5x slower so far
    uint32_t last_launches = 0;
 
    std::vector<std::unique_ptr<HostStore>> stores;
