@@ -252,6 +252,15 @@ def main():
         t = torch.tensor([device_ms, e2e_s], dtype=torch.float64, device=counts.device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         device_ms, e2e_s = float(t[0]), float(t[1])
+        # roofline line: the rank whose container scan has the most bytes (rank 0 may own no selected partition at all)
+        mine = torch.tensor([float(local_k1_bytes), k1_ms, float(k1_launches), k1_alone_ms, float(k1_alone_launches)], dtype=torch.float64, device=counts.device)
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        best = max(range(world), key=lambda r: float(every[r][0]))
+        local_k1_bytes, k1_ms, k1_launches, k1_alone_ms, k1_alone_launches = (float(x) for x in every[best])
+        local_k1_bytes, roofline_rank = int(local_k1_bytes), best
+    else:
+        roofline_rank = 0
 
     if rank == 0:
         peak, peak_source = measured_peak()
@@ -261,7 +270,7 @@ def main():
         traffic = None
         traffic_file = ROOT / "profiles" / "k1_traffic.json"
         if traffic_file.exists():
-            traffic = json.loads(traffic_file.read_text()).get(str(args.rows))
+            traffic = json.loads(traffic_file.read_text()).get(str(args.rows)) if world == 1 else None
         stats = pysilo.pool_stats(engine)
         d2h_extra = 0
         line = {
@@ -274,7 +283,7 @@ def main():
                     "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps + d2h_extra, "ms_per_step": e2e_s * 1e3 / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k1_and_popcount", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_source, "algorithmic_bytes_per_launch": local_k1_bytes, "avg_launch_ms": k1_avg_ms,
+                         "peak_source": peak_source, "rank": roofline_rank, "algorithmic_bytes_per_launch": local_k1_bytes, "avg_launch_ms": k1_avg_ms,
                          "avg_launch_ms_overlapped": k1_instep_ms, "achieved_overlapped": local_k1_bytes / (k1_instep_ms * 1e-3) / 1e9 if k1_instep_ms > 0 else 0.0,
                          "timing": "CUDA events around the launch on the library stream; avg_launch_ms with the query's kernels serialised (sb_set_overlap 0), _overlapped as they run in the timed steps",
                          "share_of_step": k1_instep_ms / (device_ms / args.steps) if device_ms else None},
