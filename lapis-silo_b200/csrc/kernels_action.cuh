@@ -214,8 +214,8 @@ constexpr uint32_t K2_MAX_WINDOW = 49152;   // positions per shared-memory diffe
 // grid: (row blocks, listed partitions, position windows). `plist` = partitions to process; a block owns
 // `rows_per_block` rows of one partition (the host sizes it so that the grid is about one wave).
 __global__ void __launch_bounds__(K2_THREADS)
-k2_missing(const SeqDev s, const PartQuery* __restrict__ pq, const uint32_t* __restrict__ plist, uint32_t* __restrict__ counts,
-           uint32_t window, uint32_t rows_per_block, int full_mode) {
+k2_missing(const SeqDev s, const PartQuery* __restrict__ pq, const uint32_t* __restrict__ plist, uint32_t* __restrict__ acc,
+           uint32_t window, uint32_t rows_per_block) {
    extern __shared__ int diff[];   // [window + 1]
    __shared__ int warp_sums[32];
    __shared__ uint32_t n_filtered_s;
@@ -278,18 +278,32 @@ k2_missing(const SeqDev s, const PartQuery* __restrict__ pq, const uint32_t* __r
    for (uint32_t i = begin; i < end; ++i) { running += diff[i]; diff[i] = running; }
    __syncthreads();
 
-   const int8_t* deleted = s.deleted + size_t(partition) * s.length;
-   const int8_t* flipped = s.flipped + size_t(partition) * s.length;
-   for (uint32_t i = threadIdx.x; i < width; i += blockDim.x) {   // coalesced over positions
-      const uint32_t pos = w0 + i;
-      const int d = deleted[pos], f = flipped[pos];
-      if (d >= 0) {
-         uint32_t add = n_filtered - uint32_t(diff[i]);          // |F| - #{i in F : pos in M_i}
-         if (f >= 0 && !full_mode) add -= n_filtered;              // deleted -= |F| part of the flipped symbol's count
-         if (add) atomicAdd(counts + size_t(d) * s.length + pos, add);
-      }
-      if (f >= 0) atomicAdd(counts + size_t(f) * s.length + pos, n_filtered);
+   // hand the block's per-position counts to the per-partition accumulator: only positions that some filtered row
+   // misses carry a value (the ends of the genome and scattered stretches), so this is far fewer atomics than positions
+   uint32_t* mine = acc + size_t(blockIdx.y) * (s.length + 1);
+   for (uint32_t i = threadIdx.x; i < width; i += blockDim.x) {
+      const int v = diff[i];
+      if (v != 0) atomicAdd(mine + w0 + i, uint32_t(v));
    }
+   if (threadIdx.x == 0 && blockIdx.z == 0) atomicAdd(mine + s.length, n_filtered);
+}
+
+// acc[j][pos] = #{i in F_p : pos in M_i}, acc[j][L] = |F_p| for the j-th listed partition p  ->  the |F| terms of the
+// deleted / flipped symbols (mutations.cpp:74-83, 111-133). grid: (ceil(L / 256), listed partitions)
+__global__ void k2_finish(const SeqDev s, const uint32_t* __restrict__ plist, const uint32_t* __restrict__ acc, uint32_t* __restrict__ counts, int full_mode) {
+   const uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+   if (pos >= s.length) return;
+   const uint32_t* mine = acc + size_t(blockIdx.y) * (s.length + 1);
+   const uint32_t n_filtered = mine[s.length];
+   if (n_filtered == 0) return;
+   const uint32_t partition = plist[blockIdx.y];
+   const int d = s.deleted[size_t(partition) * s.length + pos], f = s.flipped[size_t(partition) * s.length + pos];
+   if (d >= 0) {
+      uint32_t add = n_filtered - mine[pos];                    // |F| - #{i in F : pos in M_i}
+      if (f >= 0 && !full_mode) add -= n_filtered;              // deleted -= |F| part of the flipped symbol's count
+      if (add) atomicAdd(counts + size_t(d) * s.length + pos, add);
+   }
+   if (f >= 0) atomicAdd(counts + size_t(f) * s.length + pos, n_filtered);
 }
 
 // ---- row selection (mutations.cpp:196-215) --------------------------------------------------------------

@@ -88,7 +88,7 @@ struct sb_db {
    std::vector<Column> columns;
 
    PinnedBuffer staging, counts_host;
-   GrowDevice blob, scratch, action_scratch, table_scratch;
+   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc;
    sb_pool_stats stats{};
 
    ~sb_db() {
