@@ -58,7 +58,7 @@ void* silo_engine_handle(void* engine) { return static_cast<DeviceDatabase*>(eng
 // QueryEngine::executeQuery (query_engine.cpp:30-68) -> {"queryResult": [...]}
 char* silo_engine_execute(void* engine, const char* query_json) {
    char* out = nullptr;
-   capi::guarded([&] { out = capi::dupString(dumpJson(static_cast<DeviceDatabase*>(engine)->executeQuery(query_json))); });
+   capi::guarded([&] { out = capi::dupString(static_cast<DeviceDatabase*>(engine)->executeQueryJson(query_json)); });
    return out;
 }
 

@@ -7,6 +7,7 @@
 //   * runs M5/M6 of the Mutations action (thresholds, double division, rows) and Aggregated's row.
 // There is no CPU evaluation of operators here: sb_* failures surface as exceptions.
 #pragma once
+#include <charconv>
 #include <chrono>
 #include <deque>
 #include <unordered_map>
@@ -295,6 +296,52 @@ class DeviceDatabase {
          }
          return result;
       });
+   }
+
+   // The response body {"queryResult": [...]} of a query. Mutations without orderByFields / limit / offset -- the common
+   // case -- is written straight from the selected rows (the same text as dumpJson(executeQuery(...)): keys in the
+   // order of the entry map, doubles through json::Value::writeDouble); everything else takes the general path.
+   std::string executeQueryJson(const std::string& query_string) const {
+      HostTrace trace;
+      Query query = parseQuery(query_string);
+      const Action& action = query.action;
+      if (action.type == ActionType::AGGREGATED || !action.order_by_fields.empty() || action.limit || action.offset) return dumpJson(executeQuery(query_string));
+      trace.lap("parse");
+      action.validateOrderByFields();
+      EvaluatedFilters filters = evaluateFilter(*query.filter);
+      trace.lap("filter");
+      const int alphabet_id = action.alphabetId();
+      const Alphabet& alphabet = alphabetById(alphabet_id);
+      std::string out = "{\"queryResult\":[";
+      std::vector<sb_mutation_row> rows;
+      bool first = true;
+      char number[16];
+      for (const auto& name : mutationSequenceNames(action)) {
+         if (!mutationRows(filters, name, alphabet_id, action.min_proportion, rows)) continue;
+         trace.lap("counts+select");
+         const auto& reference = db.getReferences(alphabet_id).at(name);
+         std::string quoted_name;
+         json::Value::writeString(quoted_name, name);
+         out.reserve(out.size() + rows.size() * (80 + quoted_name.size()));
+         for (const auto& row : rows) {
+            if (!first) out += ',';
+            first = false;
+            out += "{\"count\":";
+            out.append(number, std::to_chars(number, number + sizeof number, static_cast<int32_t>(row.count)).ptr);
+            out += ",\"mutation\":\"";
+            out += alphabet.symbolToChar(reference[row.position]);
+            out.append(number, std::to_chars(number, number + sizeof number, row.position + 1).ptr);
+            out += alphabet.symbolToChar(Symbol(row.symbol));
+            out += "\",\"proportion\":";
+            json::Value::writeDouble(out, static_cast<double>(row.count) / static_cast<double>(row.total));
+            out += ",\"sequenceName\":";
+            out += quoted_name;
+            out += '}';
+         }
+         trace.lap("rows");
+      }
+      out += "]}";
+      return out;
    }
 
   private:
