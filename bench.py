@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=int(os.environ.get("SILO_BENCH_ROWS", 10_000_000)))
     ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x51100003)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--in-flight", type=int, default=8, help="queries in flight of the extra throughput measurement (N = 1 only; 0 = skip)")
     return ap.parse_args()
 
 
@@ -229,6 +230,36 @@ def main():
         barrier()
         launches = pysilo.launch_count(engine) - launches0
         k1_ms, k1_launches = pysilo.k1_accumulated(engine, reset=True)
+        # ---- throughput with several queries in flight: host threads, one library lane (streams + scratch) each ----
+        throughput = None
+        if world == 1 and args.in_flight > 1:
+            q_threads = args.in_flight
+            per_thread = max(25, (16 * args.steps + q_threads - 1) // q_threads)
+            tables = [torch.zeros(table_len, dtype=torch.int32, device=counts.device) for _ in range(q_threads)]
+
+            def concurrent(work):
+                start = threading.Barrier(q_threads + 1)
+                def loop(k):
+                    work(k)                                   # binds the thread to its lane, grows the lane's buffers
+                    start.wait()
+                    for _ in range(per_thread):
+                        work(k)
+                threads = [threading.Thread(target=loop, args=(k,)) for k in range(q_threads)]
+                for t in threads:
+                    t.start()
+                torch.cuda.synchronize()
+                start.wait()
+                pysilo.timer_begin(engine)
+                w = time.perf_counter()
+                for t in threads:
+                    t.join()
+                ms = pysilo.timer_end(engine)                  # every call is synchronous: all GPU work is done here
+                return q_threads * per_thread / (ms * 1e-3), q_threads * per_thread / (time.perf_counter() - w)
+
+            dev_qps, _ = concurrent(lambda k: prepared.run_device(0, tables[k].data_ptr(), table_len))
+            _, e2e_qps = concurrent(lambda k: engine.execute_text(query_bytes))
+            throughput = {"queries_in_flight": q_threads, "queries": q_threads * per_thread, "value": dev_qps, "e2e_value": e2e_qps, "unit": UNIT,
+                          "how": "host threads calling the same entry points concurrently; device-resident replay timed with CUDA events, e2e by wall clock"}
         # ---- the container scan timed alone (kernels of a query serialised on one stream): the roofline line ----
         pysilo.set_overlap(engine, False)
         for _ in range(2):
@@ -287,6 +318,7 @@ def main():
                          "avg_launch_ms_overlapped": k1_instep_ms, "achieved_overlapped": local_k1_bytes / (k1_instep_ms * 1e-3) / 1e9 if k1_instep_ms > 0 else 0.0,
                          "timing": "CUDA events around the launch on the library stream; avg_launch_ms with the query's kernels serialised (sb_set_overlap 0), _overlapped as they run in the timed steps",
                          "share_of_step": k1_instep_ms / (device_ms / args.steps) if device_ms else None},
+            "throughput": throughput,
             "scan_gb_per_s": info["alg_bytes"] / (device_ms / args.steps * 1e-3) / 1e9,
             "algorithmic_bytes_per_query": info["alg_bytes"],
             "clocks": clocks.summary(),

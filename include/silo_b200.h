@@ -26,6 +26,10 @@
 extern "C" {
 #endif
 
+/* Threading: after sb_db_finalize every query entry point may be called from several host threads at once, like the
+ * reference's request handlers on its immutable Database. A calling thread is bound to one of 8 lanes (own CUDA streams
+ * and scratch buffers); calls on different lanes overlap on the GPU, calls that share a lane are serialised. Every call
+ * is synchronous: results are complete when it returns. */
 typedef struct sb_db sb_db;         /* device-resident index of the partitions owned by this GPU   */
 typedef struct sb_result sb_result; /* filter result of one partition: dense device bitset + |F|   */
 

@@ -1,6 +1,7 @@
 // libsilo_b200.so — C ABI (include/silo_b200.h) over the sm_100a kernels. One translation unit:
 // this file holds the database object and the ingest / finalize entry points, api_filter.inc the
 // filter evaluation (replaces Operator::evaluate), api_action.inc the Mutations / Aggregated actions.
+#include <atomic>
 #include "common.cuh"
 #include "kernels_action.cuh"
 #include "kernels_scan.cuh"
@@ -59,21 +60,51 @@ struct sb_result {
    uint64_t cardinality;
 };
 
+// One query in flight = one lane: its own streams, events and scratch buffers. A calling thread is bound to a lane
+// (round robin); calls of different threads overlap on the GPU, calls on one lane are serialised by its mutex.
+struct sb_lane {
+   std::mutex mutex;
+   cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: kernels independent of the main chain (fork / join through events)
+   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr;
+   bool timing_valid = false, k1_ran = false;
+   uint32_t last_launches = 0;
+   PinnedBuffer staging, counts_host;
+   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc, row_area;
+   void create() {
+      SB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+      SB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+      SB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+      SB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+      SB_CUDA(cudaEventCreate(&ev_begin));
+      SB_CUDA(cudaEventCreate(&ev_k1_begin));
+      SB_CUDA(cudaEventCreate(&ev_k1_end));
+      SB_CUDA(cudaEventCreate(&ev_end));
+   }
+   ~sb_lane() {
+      if (ev_fork) { cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); }
+      if (stream2) cudaStreamDestroy(stream2);
+      if (stream) cudaStreamDestroy(stream);
+   }
+};
+constexpr uint32_t SB_LANES = 8;
+
 struct sb_db {
    int device = 0, sm_count = 148;
    uint32_t n_partitions = 0;
    bool finalized = false;
    std::mutex mutex;
-   cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: kernels independent of the main chain (fork / join through events)
-   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-   cudaEvent_t ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr, ev_timer_begin = nullptr, ev_timer_end = nullptr;
-   uint64_t launch_count = 0, k1_launches = 0, h2d_bytes = 0, d2h_bytes = 0;
+   std::vector<std::unique_ptr<sb_lane>> lanes;
+   std::atomic<uint32_t> next_lane{0};
+   sb_lane* last_timed = nullptr;
+   std::mutex k1_mutex;
+   cudaEvent_t ev_timer_begin = nullptr, ev_timer_end = nullptr;
+   std::atomic<uint64_t> launch_count{0}, h2d_bytes{0}, d2h_bytes{0};
+   uint64_t k1_launches = 0;
    double k1_total_ms = 0;
-   bool timing_valid = false, k1_ran = false, overlap = true;
+   bool overlap = true;
    uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of the scan (0 = one per SM)
    bool classic_k1 = getenv("SB_K1_SCAN") == nullptr;   // default: one CTA per work item (k1_and_popcount). SB_K1_SCAN=1: the experimental persistent
                                                         // producer/consumer pipeline (kernels_scan.cuh) -- bit-exact, but 2.5x slower so far
-   uint32_t last_launches = 0;
 
    std::vector<std::unique_ptr<HostStore>> stores;
    std::vector<std::unique_ptr<Sequence>> seqs;
@@ -87,22 +118,24 @@ struct sb_db {
    DeviceBuffer<uint16_t> d_reg_pool;
    std::vector<Column> columns;
 
-   PinnedBuffer staging, counts_host;
-   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc;
    sb_pool_stats stats{};
 
    ~sb_db() {
       cudaSetDevice(device);
       for (auto& c : columns) if (c.device) cudaFree(c.device);
-      if (ev_begin) { cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); cudaEventDestroy(ev_timer_begin); cudaEventDestroy(ev_timer_end); }
-      if (ev_fork) { cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); }
-      if (stream2) cudaStreamDestroy(stream2);
-      if (stream) cudaStreamDestroy(stream);
+      if (ev_timer_begin) { cudaEventDestroy(ev_timer_begin); cudaEventDestroy(ev_timer_end); }
+      lanes.clear();
    }
 };
 
 namespace sb {
 inline void useDevice(const sb_db* db) { SB_CUDA(cudaSetDevice(db->device)); }
+// the lane of the calling thread (threads are numbered in the order in which they first call in)
+inline sb_lane* laneOf(sb_db* db) {
+   static std::atomic<uint32_t> next_thread{0};
+   thread_local uint32_t my_index = next_thread.fetch_add(1);
+   return db->lanes[my_index % db->lanes.size()].get();
+}
 }
 
 extern "C" {
@@ -125,20 +158,13 @@ int sb_db_create(int device, uint32_t n_partitions, sb_db** out) {
       db->device = device;
       SB_CUDA(cudaDeviceGetAttribute(&db->sm_count, cudaDevAttrMultiProcessorCount, device));
       db->n_partitions = n_partitions;
-      SB_CUDA(cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking));
-      SB_CUDA(cudaStreamCreateWithFlags(&db->stream2, cudaStreamNonBlocking));
-      SB_CUDA(cudaEventCreateWithFlags(&db->ev_fork, cudaEventDisableTiming));
-      SB_CUDA(cudaEventCreateWithFlags(&db->ev_join, cudaEventDisableTiming));
+      for (uint32_t k = 0; k < SB_LANES; ++k) { db->lanes.push_back(std::make_unique<sb_lane>()); db->lanes.back()->create(); }
       {  // keep freed result slabs in the stream-ordered pool: a query must not pay for cudaMalloc
          cudaMemPool_t pool;
          SB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
          uint64_t threshold = ~0ULL;
          SB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
       }
-      SB_CUDA(cudaEventCreate(&db->ev_begin));
-      SB_CUDA(cudaEventCreate(&db->ev_k1_begin));
-      SB_CUDA(cudaEventCreate(&db->ev_k1_end));
-      SB_CUDA(cudaEventCreate(&db->ev_end));
       SB_CUDA(cudaEventCreate(&db->ev_timer_begin));
       SB_CUDA(cudaEventCreate(&db->ev_timer_end));
       db->stats.n_partitions = n_partitions;
@@ -150,7 +176,7 @@ int sb_db_free(sb_db* db) {
    return guarded([&] {
       if (!db) return;
       cudaSetDevice(db->device);
-      cudaStreamSynchronize(db->stream);
+      cudaDeviceSynchronize();
       delete db;
    });
 }

@@ -239,3 +239,28 @@ def test_full_size_properties_10m(libs):
     finally:
         engine.close()
         db.close()
+
+
+def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
+    """Eight host threads issue different queries at once (one library lane each): every result equals its sequential result."""
+    import threading
+    filters = synthetic_filters(synth_medium)
+    queries = [{"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": filters[k % len(filters)]} for k in range(8)]
+    expected = [(medium_engine.mutation_counts(q, "main", 16 * 29903)[0], medium_engine.execute(q)) for q in queries]
+    failures = []
+
+    def work(k):
+        try:
+            for _ in range(5):
+                table, _ = medium_engine.mutation_counts(queries[k], "main", 16 * 29903)
+                if not np.array_equal(table, expected[k][0]) or medium_engine.execute(queries[k]) != expected[k][1]:
+                    failures.append(k)
+        except Exception as e:   # noqa: BLE001
+            failures.append((k, repr(e)))
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert failures == []
