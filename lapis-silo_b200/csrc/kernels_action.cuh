@@ -12,8 +12,27 @@
 
 namespace sb {
 
-constexpr int K1_THREADS = 256;    // 8 warps; up to 4 CTAs per SM (48-57 KB of shared memory each)
-constexpr int K1_UNROLL = 4;       // 128-bit posting loads in flight per thread
+// tuning knobs of the container scan; the defaults are the measured best (tools/k1_experiment.py builds variants with -D)
+#ifndef SB_K1_THREADS
+#define SB_K1_THREADS 256
+#endif
+#ifndef SB_K1_UNROLL
+#define SB_K1_UNROLL 4
+#endif
+#ifndef SB_K1_MIN_CTAS
+#define SB_K1_MIN_CTAS 4
+#endif
+constexpr int K1_THREADS = SB_K1_THREADS;   // 8 warps; up to 4 CTAs per SM (48-57 KB of shared memory each)
+constexpr int K1_UNROLL = SB_K1_UNROLL;     // 128-bit posting loads in flight per thread
+#ifdef SB_K1_TIMELINE
+// diagnostics build only: per-CTA time stamps {smid, start, filter ready, warp 0 out of units, after the barrier, end, units, weight}
+__device__ unsigned long long* g_k1_timeline = nullptr;
+__device__ __forceinline__ unsigned long long globalTimerNs() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ uint32_t smId() { uint32_t v; asm volatile("mov.u32 %0, %%smid;" : "=r"(v)); return v; }
+#define K1_STAMP(k) do { if (g_k1_timeline && threadIdx.x == 0) g_k1_timeline[size_t(blockIdx.x) * 8 + (k)] = globalTimerNs(); } while (0)
+#else
+#define K1_STAMP(k) do { } while (0)
+#endif
 constexpr uint32_t K1_FILTER_BYTES = SLAB_WORDS32 * 4;
 
 __device__ __forceinline__ uint32_t laneId() { return threadIdx.x & 31; }
@@ -42,6 +61,17 @@ __device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
       "bra MBAR_WAIT;\n"
       "MBAR_DONE:\n"
       "}\n" ::"r"(smemAddr(bar)), "r"(parity) : "memory");
+}
+
+// 128-bit load of data that is read once per query
+__device__ __forceinline__ uint4 loadStream(const uint4* p) {
+#ifdef SB_K1_LDG_NOALLOC
+   uint4 v;
+   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+   return v;
+#else
+   return __ldg(p);
+#endif
 }
 
 // Adds `val` to base[idx] once per distinct idx among the lanes with pred set.
@@ -78,9 +108,10 @@ struct K1Map {
 // One CTA per work item. Shared memory: [filter slab 32 KB][tile counts (tile_slots + 1 words)][mbarrier].
 // tile_counts[sym * T + pos_in_tile] accumulates the RAW |F AND B[pos][sym]|; the flipped / deleted-symbol
 // arithmetic (mutations.cpp:85-95, 122-133) is linear in it and is applied once per slot in the flush.
-__global__ void __launch_bounds__(K1_THREADS, 4)
+__global__ void __launch_bounds__(K1_THREADS, SB_K1_MIN_CTAS)
 k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map map, uint32_t* __restrict__ counts, int full_mode) {
    extern __shared__ __align__(128) uint8_t k1_smem[];
+   K1_STAMP(1);
    const WorkItem item = s.items[__ldg(map.item_list + blockIdx.x)];
    const SlabRec slab{item.partition, item.key0};
    const uint32_t* filter32 = slab.partition < K1_INLINE_PARTITIONS ? map.inline_filter[slab.partition] : pq[slab.partition].filter32;
@@ -123,7 +154,7 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
       if (unit < n_large_units || unit >= n_units) return;
       const uint32_t base = (unit - n_large_units) * CHUNK4 + lane;
 #pragma unroll
-      for (int k = 0; k < K1_UNROLL; ++k) dst[k] = base + k * 32 < n4 ? __ldg(post4 + base + k * 32) : none;
+      for (int k = 0; k < K1_UNROLL; ++k) dst[k] = base + k * 32 < n4 ? loadStream(post4 + base + k * 32) : none;
    };
    auto grab = [&]() {
       uint32_t next = 0;
@@ -135,6 +166,7 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    if (threadIdx.x == 0) *next_unit = N_WARPS;
    __syncthreads();      // counts zeroed, mbarrier and unit counter initialised
    mbarWait(bar, 0);
+   K1_STAMP(2);
 
    auto probe = [&](uint32_t p) {
       if ((filter_s[(p >> 5) & (SLAB_WORDS32 - 1)] >> (p & 31)) & 1u) atomicAdd(&tile_counts[p >> POSTING_ROW_BITS], 1u);
@@ -158,13 +190,19 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
             }
          } else if (half == 0 && k_kind == KIND_ARRAY) {
             const uint32_t* fk = filter_s + k_local * 2048u;
-            for (uint32_t i = lane; i * 8 < k_size; i += 32) {
-               const uint4 x = __ldg(src + i);
-               const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
+            const uint32_t n_vec = (k_size + 7) >> 3;
+            for (uint32_t i0 = lane; i0 < n_vec; i0 += 128) {      // four 128-bit loads per lane in flight
+               uint4 x[4];
 #pragma unroll
-               for (uint32_t t = 0; t < 8; ++t) {
-                  const uint32_t val = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
-                  if (i * 8 + t < k_size) c2 += (fk[val >> 5] >> (val & 31)) & 1u;
+               for (uint32_t k = 0; k < 4; ++k) x[k] = i0 + k * 32 < n_vec ? __ldg(src + i0 + k * 32) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+               for (uint32_t k = 0; k < 4; ++k) {
+                  const uint32_t wv[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
+#pragma unroll
+                  for (uint32_t t = 0; t < 8; ++t) {
+                     const uint32_t val = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
+                     if ((i0 + k * 32) * 8 + t < k_size) c2 += (fk[val >> 5] >> (val & 31)) & 1u;
+                  }
                }
             }
          } else if (half == 0) {   // long run container: two rank lookups per run
@@ -190,7 +228,9 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
          unit = next;
       }
    }
+   K1_STAMP(3);
    __syncthreads();
+   K1_STAMP(4);
    // (3) flush: thread = position of the tile; symbol rows of counts[sym][pos] get coalesced REDs
    static_assert(TILE_POSITIONS <= K1_THREADS, "one flush position per thread");
    if (threadIdx.x < T && flush_pos < s.length) {
@@ -205,6 +245,14 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
       }
       if (flush_del >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(flush_del) * s.length + flush_pos, uint32_t(acc_deleted));
    }
+#ifdef SB_K1_TIMELINE
+   if (g_k1_timeline && threadIdx.x == 0) {
+      g_k1_timeline[size_t(blockIdx.x) * 8 + 0] = smId();
+      g_k1_timeline[size_t(blockIdx.x) * 8 + 5] = globalTimerNs();
+      g_k1_timeline[size_t(blockIdx.x) * 8 + 6] = (uint64_t(n_large_units) << 32) | n_units;
+      g_k1_timeline[size_t(blockIdx.x) * 8 + 7] = 16ull * n4;
+   }
+#endif
 }
 
 // ---- K2 ---------------------------------------------------------------------------------------------

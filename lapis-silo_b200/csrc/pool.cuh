@@ -140,6 +140,12 @@ inline uint64_t itemWeightCap() {   // bytes of postings + large payload per Mut
    return (e && atoi(e) > 0 ? uint64_t(atoi(e)) : 128) * 1024;
 }
 
+inline uint32_t arraySplit() {   // values per large-array entry (SB_ARRAY_SPLIT: tuning; a multiple of 8 keeps the pieces 16-byte aligned)
+   const char* e = getenv("SB_ARRAY_SPLIT");
+   const uint32_t v = e && atoi(e) >= 64 ? uint32_t(atoi(e)) : 1024u;
+   return (v + 7u) & ~7u;
+}
+
 // Packs the ingested stores of one sequence into the tiled device layout.
 inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>& stores, uint32_t n_partitions, sb_pool_stats& stats) {
    const uint32_t sigma = seq.sigma, tp = seq.tile_positions, L = seq.length;
@@ -175,6 +181,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    uint64_t hist[16] = {};   // SB_TRACE: array cardinalities 1,2,3,4,<=8,<=16,<=32,<=64,<=256,<=4096 | runs | bitsets
    const uint32_t filler = slots_per_tile << POSTING_ROW_BITS;
    const uint64_t item_cap = itemWeightCap();
+   const uint32_t array_split = arraySplit();
    for (uint32_t tile = 0; tile < seq.n_tiles; ++tile) {
       const uint32_t slot_end = (tile + 1) * slots_per_tile;
       for (uint32_t slab_id = 0; slab_id < n_slabs; ++slab_id) {
@@ -215,13 +222,19 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
             } else if (c.kind == KIND_RUN && cardinality <= FLAT_MAX) {
                for (uint32_t r = 0; r < c.size; ++r) for (uint32_t v = src[2 * r], last = uint32_t(src[2 * r]) + src[2 * r + 1]; v <= last; ++v) postings.push_back(head | v);
             } else {
-               const uint32_t n16 = c.kind == KIND_BITSET ? 4096 : c.kind == KIND_ARRAY ? c.size : 2 * c.size;
-               const size_t at = large_pool.size();
-               SB_REQUIRE(at / 2 < 0xFFFFFFFFull, "large pool beyond 64 GB");
-               large_pool.resize(at + size_t((n16 + 7) / 8) * 2, 0);
-               memcpy(large_pool.data() + at, src, size_t(n16) * 2);
-               large_entries.push_back({uint32_t(at / 2), c.size, pk.slot2 | (uint32_t(c.kind) << 14) | (key_local << 16), 0});
-               large_bytes += 16 + uint64_t((n16 + 7) / 8) * 16;
+               // a big array container becomes several entries of at most `array_split` values: an entry is one warp's unit of
+               // work in the scan, and a 4,096-value array in one piece is a straggler (set semantics: the pieces are disjoint)
+               const uint32_t n16_all = c.kind == KIND_BITSET ? 4096 : c.kind == KIND_ARRAY ? c.size : 2 * c.size;
+               const uint32_t piece = c.kind == KIND_ARRAY ? array_split : n16_all;
+               for (uint32_t first = 0; first < n16_all; first += piece) {
+                  const uint32_t n16 = std::min(piece, n16_all - first);
+                  const size_t at = large_pool.size();
+                  SB_REQUIRE(at / 2 < 0xFFFFFFFFull, "large pool beyond 64 GB");
+                  large_pool.resize(at + size_t((n16 + 7) / 8) * 2, 0);
+                  memcpy(large_pool.data() + at, src + first, size_t(n16) * 2);
+                  large_entries.push_back({uint32_t(at / 2), c.kind == KIND_ARRAY ? n16 : c.size, pk.slot2 | (uint32_t(c.kind) << 14) | (key_local << 16), 0});
+                  large_bytes += 16 + uint64_t((n16 + 7) / 8) * 16;
+               }
             }
          }
          // cut the segment into weight-bounded work items: postings and large entries are split evenly

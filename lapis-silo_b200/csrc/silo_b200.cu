@@ -103,6 +103,7 @@ struct sb_db {
    double k1_total_ms = 0;
    bool overlap = true;
    uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of the scan (0 = one per SM)
+   uint32_t k1_pad_bytes = getenv("SB_K1_PAD_KB") ? uint32_t(atoi(getenv("SB_K1_PAD_KB"))) * 1024u : 0;   // experiments: extra dynamic shared memory per CTA (fewer CTAs per SM, more L1)
    bool classic_k1 = getenv("SB_K1_SCAN") == nullptr;   // default: one CTA per work item (k1_and_popcount). SB_K1_SCAN=1: the experimental persistent
                                                         // producer/consumer pipeline (kernels_scan.cuh) -- bit-exact, but 2.5x slower so far
 
@@ -315,3 +316,23 @@ int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, 
 
 #include "api_filter.inc"
 #include "api_action.inc"
+
+#ifdef SB_K1_TIMELINE
+// diagnostics build (tools/k1_experiment.py): per-CTA time stamps of the container scan
+extern "C" int sb_debug_timeline_enable(uint32_t max_blocks) {
+   return guarded([&] {
+      unsigned long long* buf = nullptr;
+      SB_CUDA(cudaMalloc(reinterpret_cast<void**>(&buf), size_t(max_blocks) * 64));
+      SB_CUDA(cudaMemset(buf, 0, size_t(max_blocks) * 64));
+      SB_CUDA(cudaMemcpyToSymbol(g_k1_timeline, &buf, sizeof(buf)));
+   });
+}
+extern "C" int sb_debug_timeline_read(uint64_t* out, uint32_t blocks) {
+   return guarded([&] {
+      SB_CUDA(cudaDeviceSynchronize());
+      unsigned long long* buf = nullptr;
+      SB_CUDA(cudaMemcpyFromSymbol(&buf, g_k1_timeline, sizeof(buf)));
+      SB_CUDA(cudaMemcpy(out, buf, size_t(blocks) * 64, cudaMemcpyDeviceToHost));
+   });
+}
+#endif

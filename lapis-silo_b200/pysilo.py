@@ -14,6 +14,8 @@ import numpy as np
 
 PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
+# kernel experiments (tools/k1_experiment.py) load a variant build of both libraries from another directory
+LIBDIR = Path(os.environ["SILO_B200_LIBDIR"]).resolve() if os.environ.get("SILO_B200_LIBDIR") else PKG
 SIGMA = {0: 16, 1: 25}
 
 _host = None
@@ -30,10 +32,10 @@ def host():
     if _host is not None:
         return _host
     for name in ("libsilo_b200.so", "libsilo_host.so"):
-        if not (PKG / name).exists():
+        if not (LIBDIR / name).exists():
             raise RuntimeError(f"{name} is not built: run `make -C {PKG}` (there is no fallback path)")
-    ctypes.CDLL(str(PKG / "libsilo_b200.so"), mode=ctypes.RTLD_GLOBAL)
-    lib = ctypes.CDLL(str(PKG / "libsilo_host.so"), mode=ctypes.RTLD_GLOBAL)
+    ctypes.CDLL(str(LIBDIR / "libsilo_b200.so"), mode=ctypes.RTLD_GLOBAL)
+    lib = ctypes.CDLL(str(LIBDIR / "libsilo_host.so"), mode=ctypes.RTLD_GLOBAL)
     vp, cp, u32, u64, sz = ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_size_t
     pu32 = ctypes.POINTER(ctypes.c_uint32)
     sig = {
@@ -236,7 +238,7 @@ class PoolStats(ctypes.Structure):
 
 def _sb():
     host()
-    lib = ctypes.CDLL(str(PKG / "libsilo_b200.so"))
+    lib = ctypes.CDLL(str(LIBDIR / "libsilo_b200.so"))
     lib.sb_last_error.restype = ctypes.c_char_p
     for name in ("sb_timer_begin", "sb_timer_end", "sb_launch_count", "sb_k1_accumulated", "sb_pool_get_stats", "sb_transfer_bytes"):
         getattr(lib, name).restype = ctypes.c_int
