@@ -121,7 +121,7 @@ struct PartQuery {
 struct SeqDev {
    const uint32_t* postings;
    const LargeEntry* large_entries;
-   const WorkItem* items;       // ordered by (partition, weight descending)
+   const WorkItem* items;       // ordered by slab (hence partition), then tile
    const SegRec* segs;          // [n_tiles * n_slabs + 1]
    const SlabRec* slabs;        // [n_slabs]
    const uint32_t* slab_begin;  // [P + 1] first slab of each partition

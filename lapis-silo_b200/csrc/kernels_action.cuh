@@ -19,6 +19,9 @@ namespace sb {
 #ifndef SB_K1_UNROLL
 #define SB_K1_UNROLL 4
 #endif
+#ifndef SB_K1_PROBE
+#define SB_K1_PROBE 0
+#endif
 #ifndef SB_K1_MIN_CTAS
 #define SB_K1_MIN_CTAS 4
 #endif
@@ -34,6 +37,8 @@ __device__ __forceinline__ uint32_t smId() { uint32_t v; asm volatile("mov.u32 %
 #define K1_STAMP(k) do { } while (0)
 #endif
 constexpr uint32_t K1_FILTER_BYTES = SLAB_WORDS32 * 4;
+// count table of a tile in shared memory: tile_slots counters + 32 dummy slots (one per lane: where the misses go)
+__host__ __device__ constexpr uint32_t k1TableWords(uint32_t tile_slots) { return (tile_slots + 32 + 1) & ~1u; }
 
 __device__ __forceinline__ uint32_t laneId() { return threadIdx.x & 31; }
 __device__ __forceinline__ uint32_t laneMaskLt() { return (1u << laneId()) - 1u; }
@@ -119,7 +124,7 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    uint32_t* filter_s = reinterpret_cast<uint32_t*>(k1_smem);
    uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES);
    const uint32_t T = s.tile_positions, tile_slots = T * s.sigma;
-   uint64_t* bar = reinterpret_cast<uint64_t*>(tile_counts + ((tile_slots + 2) & ~1u));
+   uint64_t* bar = reinterpret_cast<uint64_t*>(tile_counts + k1TableWords(tile_slots));
    uint32_t* next_unit = reinterpret_cast<uint32_t*>(bar + 1);
 
    if (threadIdx.x == 0) {
@@ -128,7 +133,7 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
       mbarExpectTx(bar, K1_FILTER_BYTES);
       bulkLoad(filter_s, filter32 + size_t(slab.key0) * 2048u, K1_FILTER_BYTES, bar);
    }
-   for (uint32_t i = threadIdx.x; i <= tile_slots; i += K1_THREADS) tile_counts[i] = 0;
+   for (uint32_t i = threadIdx.x; i < tile_slots + 32; i += K1_THREADS) tile_counts[i] = 0;
 
    // flags of this thread's flush position, fetched now so that the flush does not wait for them
    const uint32_t flush_pos = item.tile * T + threadIdx.x;
@@ -148,7 +153,8 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    const uint32_t n4 = (item.post_end - item.post_begin + 3u) >> 2;
    const uint32_t n_large_units = 2u * (item.large_end - item.large_begin);
    const uint32_t n_units = n_large_units + (n4 + CHUNK4 - 1) / CHUNK4;
-   const uint4 none = make_uint4(~0u, ~0u, ~0u, ~0u);
+   const uint32_t dummy = tile_slots << POSTING_ROW_BITS;          // a posting of the slot that is never flushed
+   const uint4 none = make_uint4(dummy, dummy, dummy, dummy);
    uint4 v[K1_UNROLL];
    auto loadChunk = [&](uint32_t unit, uint4 (&dst)[K1_UNROLL]) {
       if (unit < n_large_units || unit >= n_units) return;
@@ -168,8 +174,24 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    mbarWait(bar, 0);
    K1_STAMP(2);
 
-   auto probe = [&](uint32_t p) {
-      if ((filter_s[(p >> 5) & (SLAB_WORDS32 - 1)] >> (p & 31)) & 1u) atomicAdd(&tile_counts[p >> POSTING_ROW_BITS], 1u);
+   // Eight postings at a time: the eight filter words are fetched first (independent shared-memory loads), then the hits
+   // are counted with unconditional shared-memory increments -- no data-dependent branch, one load round trip per eight postings.
+   auto probe8 = [&](const uint4& a, const uint4& b) {
+      const uint32_t p[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      uint32_t w[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) w[t] = filter_s[(p[t] >> 5) & (SLAB_WORDS32 - 1)];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+         const bool hit = (w[t] >> (p[t] & 31)) & 1u;
+#if SB_K1_PROBE == 0      // a miss increments the lane's dummy slot: unconditional, so the compiler emits no branch
+         atomicAdd(&tile_counts[hit ? (p[t] >> POSTING_ROW_BITS) : tile_slots + lane], 1u);
+#elif SB_K1_PROBE == 1    // one dummy slot for all lanes
+         atomicAdd(&tile_counts[hit ? (p[t] >> POSTING_ROW_BITS) : tile_slots], 1u);
+#else                     // branch around the increment
+         if (hit) atomicAdd(&tile_counts[p[t] >> POSTING_ROW_BITS], 1u);
+#endif
+      }
    };
    while (unit < n_units) {
       if (unit < n_large_units) {
@@ -199,9 +221,9 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
                for (uint32_t k = 0; k < 4; ++k) {
                   const uint32_t wv[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
 #pragma unroll
-                  for (uint32_t t = 0; t < 8; ++t) {
+                  for (uint32_t t = 0; t < 8; ++t) {      // the padding of the last vector is zero: probed like a value, masked out
                      const uint32_t val = (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
-                     if ((i0 + k * 32) * 8 + t < k_size) c2 += (fk[val >> 5] >> (val & 31)) & 1u;
+                     c2 += ((fk[val >> 5] >> (val & 31)) & 1u) & uint32_t((i0 + k * 32) * 8 + t < k_size);
                   }
                }
             }
@@ -218,11 +240,8 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
          const uint32_t next = grab();
          uint4 nx[K1_UNROLL];
          loadChunk(next, nx);
-         const uint32_t base = (unit - n_large_units) * CHUNK4 + lane;
 #pragma unroll
-         for (int k = 0; k < K1_UNROLL; ++k) {
-            if (base + k * 32 < n4) { probe(v[k].x); probe(v[k].y); probe(v[k].z); probe(v[k].w); }
-         }
+         for (int k = 0; k < K1_UNROLL; k += 2) probe8(v[k], v[k + 1]);   // loads past the item's end carry postings of the dummy slot
 #pragma unroll
          for (int k = 0; k < K1_UNROLL; ++k) v[k] = nx[k];
          unit = next;

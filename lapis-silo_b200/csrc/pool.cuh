@@ -117,8 +117,11 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<uint32_t> slab_begin;
    DeviceBuffer<uint4> large_pool;
    std::vector<uint32_t> h_slab_begin;    // [P + 1]
-   std::vector<uint32_t> h_item_begin;    // [P + 1] work items of each partition (items are ordered by partition, then weight)
+   std::vector<uint32_t> h_item_begin;    // [P + 1] work items of each partition
    std::vector<uint32_t> h_item_weight;   // [n_items] bytes of postings + large payload
+   std::vector<uint64_t> h_item_prefix;   // [n_items + 1] running sum of the k1_stream cost of the items (units + KS_ITEM_COST each)
+   std::vector<uint32_t> h_slab_item_begin;   // [n_slabs + 1] items of each slab (items are ordered by slab, then tile)
+   std::vector<uint32_t> h_by_weight;     // [n_items] item indices, per partition heaviest first
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
@@ -251,21 +254,37 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
          SB_REQUIRE(postings.size() < 0xFFFFFFF0ull, "more than 2^32 postings in one sequence");
       }
    }
-   {  // order: partition, then heaviest first (the block scheduler hands out CTAs in index order, so the tail stays short)
+   {  // order: slab (hence partition), then tile: a persistent CTA of k1_stream takes consecutive items of one slab and keeps
+      // the slab's filter in shared memory. k1_and_popcount (one CTA per item) wants every partition's items heaviest
+      // first instead: h_by_weight lists them that way (the block scheduler hands out CTAs in index order).
       std::vector<uint32_t> order(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) order[k] = k;
-      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
-         const uint32_t pa = slabs[items[a].slab].partition, pb = slabs[items[b].slab].partition;
-         return pa != pb ? pa < pb : item_weight[a] > item_weight[b];
-      });
+      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return items[a].slab < items[b].slab; });   // creation order is tile-major
       std::vector<WorkItem> sorted(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) sorted[k] = items[order[k]];
       items.swap(sorted);
       seq.h_item_weight.resize(items.size());
-      for (uint32_t k = 0; k < order.size(); ++k) seq.h_item_weight[k] = uint32_t(std::min<uint64_t>(item_weight[order[k]], 0xFFFFFFFFull));
+      seq.h_item_prefix.assign(items.size() + 1, 0);
+      for (uint32_t k = 0; k < order.size(); ++k) {
+         seq.h_item_weight[k] = uint32_t(std::min<uint64_t>(item_weight[order[k]], 0xFFFFFFFFull));
+         // cost of an item in k1_stream: its units (a 2 KB posting chunk and a 4 KB bitset half take a warp about equally long)
+         // plus the flush of its count table, which costs about as much as KS_ITEM_COST units whatever the item holds
+         const WorkItem& it = items[k];
+         const uint32_t n4 = (it.post_end - it.post_begin + 3u) >> 2;
+         const uint32_t units = 2u * (it.large_end - it.large_begin) + (n4 + 32u * K1_UNROLL - 1u) / (32u * K1_UNROLL);
+         seq.h_item_prefix[k + 1] = seq.h_item_prefix[k] + units + KS_ITEM_COST;
+      }
       seq.h_item_begin.assign(n_partitions + 1, 0);
-      for (const WorkItem& it : items) seq.h_item_begin[slabs[it.slab].partition + 1]++;
+      seq.h_slab_item_begin.assign(size_t(n_slabs) + 1, 0);
+      for (const WorkItem& it : items) { seq.h_item_begin[slabs[it.slab].partition + 1]++; seq.h_slab_item_begin[it.slab + 1]++; }
       for (uint32_t p = 0; p < n_partitions; ++p) seq.h_item_begin[p + 1] += seq.h_item_begin[p];
+      for (uint32_t k = 0; k < n_slabs; ++k) seq.h_slab_item_begin[k + 1] += seq.h_slab_item_begin[k];
+      seq.h_by_weight.resize(items.size());
+      for (uint32_t k = 0; k < items.size(); ++k) seq.h_by_weight[k] = k;
+      for (uint32_t p = 0; p < n_partitions; ++p) {
+         std::stable_sort(seq.h_by_weight.begin() + seq.h_item_begin[p], seq.h_by_weight.begin() + seq.h_item_begin[p + 1],
+                          [&](uint32_t a, uint32_t b) { return seq.h_item_weight[a] > seq.h_item_weight[b]; });
+      }
    }
    while (postings.size() % 4) postings.push_back(filler);
    segs.back() = {uint32_t(postings.size()), uint32_t(large_entries.size())};

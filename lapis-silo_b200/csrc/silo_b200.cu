@@ -4,7 +4,7 @@
 #include <atomic>
 #include "common.cuh"
 #include "kernels_action.cuh"
-#include "kernels_scan.cuh"
+#include "kernels_stream.cuh"
 #include "kernels_filter.cuh"
 #include "pool.cuh"
 
@@ -102,10 +102,12 @@ struct sb_db {
    uint64_t k1_launches = 0;
    double k1_total_ms = 0;
    bool overlap = true;
-   uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of the scan (0 = one per SM)
+   uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of k1_stream (0 = one per SM)
    uint32_t k1_pad_bytes = getenv("SB_K1_PAD_KB") ? uint32_t(atoi(getenv("SB_K1_PAD_KB"))) * 1024u : 0;   // experiments: extra dynamic shared memory per CTA (fewer CTAs per SM, more L1)
-   bool classic_k1 = getenv("SB_K1_SCAN") == nullptr;   // default: one CTA per work item (k1_and_popcount). SB_K1_SCAN=1: the experimental persistent
-                                                        // producer/consumer pipeline (kernels_scan.cuh) -- bit-exact, but 2.5x slower so far
+   // container scan of the Mutations action: k1_and_popcount (one CTA per work item, kernels_action.cuh) unless SB_K1=stream
+   // selects k1_stream (one persistent CTA per SM, kernels_stream.cuh: bit-exact, but 1.6x slower so far -- DESIGN.md).
+   // Tests run both.
+   bool classic_k1 = !(getenv("SB_K1") != nullptr && std::string(getenv("SB_K1")) == "stream");
 
    std::vector<std::unique_ptr<HostStore>> stores;
    std::vector<std::unique_ptr<Sequence>> seqs;

@@ -264,3 +264,23 @@ def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
     for t in threads:
         t.join()
     assert failures == []
+
+
+@pytest.mark.parametrize("env", [{"SB_K1": "item"}, {"SB_K1": "stream"}, {"SB_K1": "stream", "SB_K1_CTAS": "1"}, {"SB_K1": "stream", "SB_K1_CTAS": "3"},
+                                 {"SB_K1": "stream", "SB_K1_CTAS": "7"}, {"SB_K1": "stream", "SB_K1_CTAS": "4000"}],
+                         ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
+def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch):
+    """both container-scan kernels (k1_and_popcount: one CTA per work item; k1_stream: persistent CTAs) and odd numbers of
+    persistent CTAs (runs that cross slabs and partitions, one CTA with everything, more CTAs than items) against the oracle"""
+    pysilo, oracle = libs
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)      # read when the device database is created
+    for db, names, sigma_tables, faithful in ((synth_small, [("main", 3000)], True, True), (synth_medium, [("main", 29903)], False, False)):
+        engine = pysilo.Engine(db, 0)
+        try:
+            for f in synthetic_filters(db)[2:5]:
+                tables_equal(libs, db, engine, {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f}, names, 16, faithful=faithful)
+                if sigma_tables:
+                    tables_equal(libs, db, engine, {"action": {"type": "AminoAcidMutations", "minProportion": 0.01}, "filterExpression": f}, sorted(GENE_LENGTH.items()), 25)
+        finally:
+            engine.close()
