@@ -2,9 +2,12 @@
 """bench.py — Mutations-action queries/s on synthetic SARS-CoV-2-shaped data (BASELINE.json).
 
 One "step" = one nucleotide Mutations query (minProportion 0.05) under the N-Of filter of BASELINE config
-C3 (3 of 10 clade-defining NucleotideEquals) over the whole database. The database (default 10 M sequences
-x 29,903 nt) is fixed; with N GPUs its DatabasePartitions are sharded over the ranks (strong scaling) and
-the per-rank count tables are summed with an NCCL reduce.
+C3 (3 of 10 clade-defining NucleotideEquals) over one shard of 10 M sequences x 29,903 nt. The path shards by
+DatabasePartition: with N GPUs every rank holds the DatabasePartitions of its own 10 M-sequence shard (weak
+scaling: an N x 10 M-sequence database; the shards are statistically identical, generated from the same seed), a
+step runs the query on every shard and sums the per-rank count tables with an NCCL reduce, and `value` counts one
+query per shard: N x steps / time (at N = 1 plainly queries/s). `--strong` instead shards ONE database of
+`--rows` sequences over the ranks (the 40 M-sequence configuration C5: `--rows 40000000 --strong`).
 
     value  queries/s with the index resident in HBM and the query compiled once: filter kernels + count
            kernels (+ NCCL reduce), timed with CUDA events on the library's stream, max over ranks
@@ -42,6 +45,7 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=int(os.environ.get("SILO_BENCH_ROWS", 10_000_000)))
     ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x51100003)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strong", action="store_true", help="N > 1: shard one database of --rows sequences over the ranks instead of one shard of --rows per rank")
     ap.add_argument("--in-flight", type=int, default=8, help="queries in flight of the extra throughput measurement (N = 1 only; 0 = skip)")
     return ap.parse_args()
 
@@ -140,8 +144,9 @@ def run_reference(args, rank, world):
     per_step = sum(times) / len(times)
     value = (sample_rows / args.rows) / per_step
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": per_step * 1e3 * args.rows / sample_rows, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32",
-            "data": "synthetic", "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt, nucleotide Mutations under N-Of(3 of 10)", "rows": args.rows},
+            "ms_per_step": per_step * 1e3 * args.rows / sample_rows, "higher_is_better": True, "scaling": "strong" if args.strong and args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic", "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt per shard, nucleotide Mutations under N-Of(3 of 10)", "rows": args.rows,
+                                            "note": "shard-queries/s of the host CPU: the same for any --gpus (the CPU answers the shards one after the other)"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": base["sample"] + " per step; the reference itself is not buildable here (DESIGN.md 2)"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -170,7 +175,10 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     t0 = time.time()
-    db = pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank)
+    weak = world > 1 and not args.strong
+    units_per_step = world if weak else 1          # shard-queries per step (weak scaling: every rank answers the query on its own shard)
+    db = pysilo.Database.synthetic(args.rows, args.seed) if weak else pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank)
+    total_rows = args.rows * (world if weak else 1)
     t_generate = time.time() - t0
     engine = pysilo.Engine(db, local_rank, db.owned)
     t_ingest = time.time() - t0 - t_generate
@@ -305,12 +313,14 @@ def main():
         stats = pysilo.pool_stats(engine)
         d2h_extra = 0
         line = {
-            "metric": METRIC, "value": args.steps / (device_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": device_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt, nucleotide Mutations under N-Of(3 of 10)", "rows": args.rows,
-                       "partitions": db.n_partitions, "partitions_on_rank0": len(db.owned), "l2": "inputs larger than L2 (container pool streamed once per query)",
-                       "parallelism": f"partitions sharded over {world} GPU(s), NCCL reduce of the count table"},
-            "e2e": {"value": args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps + len(query_json),
+            "metric": METRIC, "value": units_per_step * args.steps / (device_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": device_ms / args.steps, "higher_is_better": True, "scaling": "weak" if weak or world == 1 else "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt per shard, nucleotide Mutations under N-Of(3 of 10)", "rows": total_rows,
+                       "rows_per_rank": args.rows if weak or world == 1 else None, "shard_queries_per_step": units_per_step,
+                       "partitions": db.n_partitions * (world if weak else 1), "partitions_on_rank0": len(db.owned), "l2": "inputs larger than L2 (container pool streamed once per query)",
+                       "parallelism": (f"{world} shard(s) of {args.rows} sequences, one per GPU (DatabasePartitions are the unit of sharding); a step = the query on every shard + NCCL reduce "
+                                       f"of the count tables; value = shard-queries/s" if weak or world == 1 else f"one database of {args.rows} sequences, partitions sharded over {world} GPUs, NCCL reduce of the count table")},
+            "e2e": {"value": units_per_step * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps + len(query_json),
                     "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps + d2h_extra, "ms_per_step": e2e_s * 1e3 / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k1_and_popcount", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

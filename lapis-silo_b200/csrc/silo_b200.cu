@@ -68,8 +68,13 @@ struct sb_lane {
    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr;
    bool timing_valid = false, k1_ran = false;
    uint32_t last_launches = 0;
-   PinnedBuffer staging, counts_host;
-   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc, row_area;
+   PinnedBuffer staging, counts_host, list_staging;
+   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc, row_area, k1_list;
+   // the K1 work list that is on the device (k1_list): built for this sequence and these partial partitions
+   const void* k1_key_seq = nullptr;
+   bool k1_key_stream = false;
+   std::vector<uint32_t> k1_key_partial;
+   uint32_t k1_grid = 0;
    void create() {
       SB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
       SB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
