@@ -106,7 +106,8 @@ __device__ __forceinline__ uint32_t filterRangeCount(const PartQuery& q, uint32_
 // the bulk copy of the filter slab is one dependent load closer.
 constexpr uint32_t K1_INLINE_PARTITIONS = 64;
 struct K1Map {
-   const uint32_t* item_list;                              // [grid]
+   const uint32_t* item_list;                              // k1_stream: run table (kernels_stream.cuh)
+   const WorkItem* query_items;                            // k1_and_popcount: [grid] the query's work items, heaviest first (a copy: one dependent load less per CTA)
    const uint32_t* inline_filter[K1_INLINE_PARTITIONS];    // filter32 of partition p (p < K1_INLINE_PARTITIONS)
 };
 
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(K1_THREADS, SB_K1_MIN_CTAS)
 k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map map, uint32_t* __restrict__ counts, int full_mode) {
    extern __shared__ __align__(128) uint8_t k1_smem[];
    K1_STAMP(1);
-   const WorkItem item = s.items[__ldg(map.item_list + blockIdx.x)];
+   const WorkItem item = map.query_items[blockIdx.x];
    const SlabRec slab{item.partition, item.key0};
    const uint32_t* filter32 = slab.partition < K1_INLINE_PARTITIONS ? map.inline_filter[slab.partition] : pq[slab.partition].filter32;
 
@@ -255,12 +256,18 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
    if (threadIdx.x < T && flush_pos < s.length) {
       const uint32_t pl = threadIdx.x;
       int acc_deleted = 0;
-      for (uint32_t sym = 0; sym < s.sigma; ++sym) {
-         const int raw = int(tile_counts[sym * T + pl]);
-         if (raw == 0 || int(sym) == flush_del) continue;
-         const int add_slot = int(sym) == flush_flip ? -raw : raw;
-         atomicAdd(counts + size_t(sym) * s.length + flush_pos, uint32_t(add_slot));
-         acc_deleted += full_mode ? -raw : -add_slot;
+      for (uint32_t sym0 = 0; sym0 < s.sigma; sym0 += 8) {      // eight counters in flight, then their REDs
+         int raw[8];
+#pragma unroll
+         for (uint32_t q = 0; q < 8; ++q) raw[q] = sym0 + q < s.sigma ? int(tile_counts[(sym0 + q) * T + pl]) : 0;
+#pragma unroll
+         for (uint32_t q = 0; q < 8; ++q) {
+            const uint32_t sym = sym0 + q;
+            if (raw[q] == 0 || int(sym) == flush_del) continue;
+            const int add_slot = int(sym) == flush_flip ? -raw[q] : raw[q];
+            atomicAdd(counts + size_t(sym) * s.length + flush_pos, uint32_t(add_slot));
+            acc_deleted += full_mode ? -raw[q] : -add_slot;
+         }
       }
       if (flush_del >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(flush_del) * s.length + flush_pos, uint32_t(acc_deleted));
    }

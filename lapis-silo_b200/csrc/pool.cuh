@@ -122,6 +122,7 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    std::vector<uint64_t> h_item_prefix;   // [n_items + 1] running sum of the k1_stream cost of the items (units + KS_ITEM_COST each)
    std::vector<uint32_t> h_slab_item_begin;   // [n_slabs + 1] items of each slab (items are ordered by slab, then tile)
    std::vector<uint32_t> h_by_weight;     // [n_items] item indices, per partition heaviest first
+   std::vector<WorkItem> h_items;         // host copy of `items`
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
@@ -322,6 +323,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.postings.upload(postings);
    seq.large_entries.upload(large_entries);
    seq.items.upload(items);
+   seq.h_items = items;
    seq.segs.upload(segs);
    seq.slabs.upload(slabs);
    seq.slab_begin.upload(seq.h_slab_begin);
