@@ -69,12 +69,10 @@ struct sb_lane {
    bool timing_valid = false, k1_ran = false;
    uint32_t last_launches = 0;
    PinnedBuffer staging, counts_host, list_staging;
-   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc, row_area, k1_list;
-   // the K1 work list that is on the device (k1_list): built for this sequence and these partial partitions
-   const void* k1_key_seq = nullptr;
-   bool k1_key_stream = false;
-   std::vector<uint32_t> k1_key_partial;
-   uint32_t k1_grid = 0;
+   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc, row_area;
+   // the K1 work list of a sequence that is on the device: built for these partial partitions (rebuilt when they change)
+   struct K1List { GrowDevice device; bool valid = false, stream = false; std::vector<uint32_t> partial; uint32_t grid = 0; };
+   std::map<const void*, K1List> k1_lists;
    void create() {
       SB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
       SB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));

@@ -9,7 +9,13 @@
 #pragma once
 #include <charconv>
 #include <chrono>
+#include <atomic>
+#include <condition_variable>
 #include <deque>
+#include <exception>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <unordered_map>
 
 #include "../../include/silo_b200.h"
@@ -17,6 +23,71 @@
 #include "query.hpp"
 
 namespace silo::engine {
+
+// A few host threads that run the per-sequence parts of one query side by side (AminoAcidMutations over all genes: twelve
+// independent count tables). Every thread is bound to a lane of the library (streams + scratch of its own), so the
+// kernels of different sequences overlap on the GPU. One batch at a time; the calling thread takes part.
+class WorkerPool {
+ public:
+   explicit WorkerPool(unsigned n_threads) {
+      for (unsigned k = 0; k < n_threads; ++k) threads_.emplace_back([this] { loop(); });
+   }
+   ~WorkerPool() {
+      { std::lock_guard<std::mutex> lock(mutex_); stop_ = true; }
+      wake_.notify_all();
+      for (auto& t : threads_) t.join();
+   }
+   // runs job(0) ... job(n - 1), returns when all are done; rethrows the first exception
+   void run(size_t n, const std::function<void(size_t)>& job) {
+      std::lock_guard<std::mutex> one_batch(batch_mutex_);
+      {
+         std::lock_guard<std::mutex> lock(mutex_);
+         job_ = &job; n_ = n; next_ = 0; left_ = n; error_ = nullptr;
+      }
+      wake_.notify_all();
+      work();
+      std::unique_lock<std::mutex> lock(mutex_);
+      done_.wait(lock, [this] { return left_ == 0; });
+      job_ = nullptr;
+      if (error_) std::rethrow_exception(error_);
+   }
+
+ private:
+   void work() {
+      for (;;) {
+         size_t index;
+         const std::function<void(size_t)>* job;
+         {
+            std::lock_guard<std::mutex> lock(mutex_);
+            if (!job_ || next_ >= n_) return;
+            index = next_++;
+            job = job_;
+         }
+         std::exception_ptr error;
+         try { (*job)(index); } catch (...) { error = std::current_exception(); }
+         std::lock_guard<std::mutex> lock(mutex_);
+         if (error && !error_) error_ = error;
+         if (--left_ == 0) done_.notify_all();
+      }
+   }
+   void loop() {
+      for (;;) {
+         {
+            std::unique_lock<std::mutex> lock(mutex_);
+            wake_.wait(lock, [this] { return stop_ || (job_ && next_ < n_); });
+            if (stop_) return;
+         }
+         work();
+      }
+   }
+   std::vector<std::thread> threads_;
+   std::mutex mutex_, batch_mutex_;
+   std::condition_variable wake_, done_;
+   const std::function<void(size_t)>* job_ = nullptr;
+   size_t n_ = 0, next_ = 0, left_ = 0;
+   std::exception_ptr error_;
+   bool stop_ = false;
+};
 
 struct HostTrace {   // SB_TRACE=1: lap times of the host side on stderr (diagnostics only)
    bool on = getenv("SB_TRACE") != nullptr;
@@ -95,7 +166,7 @@ class DeviceDatabase {
       } catch (...) { sb_db_free(handle); handle = nullptr; throw; }
    }
    DeviceDatabase(const DeviceDatabase&) = delete;
-   ~DeviceDatabase() { if (handle) sb_db_free(handle); }
+   ~DeviceDatabase() { pool_.reset(); if (handle) sb_db_free(handle); }
 
    // ---- plan lowering -------------------------------------------------------------------------------
    struct Plan {
@@ -240,6 +311,20 @@ class DeviceDatabase {
       rows.resize(n);
       return produced != 0;
    }
+   // mutationRows for every sequence of the action (mutations.cpp:258-270 loops over them one after the other): the
+   // sequences are independent, so more than one runs on the worker pool, each on a lane of the library.
+   struct SequenceRows { bool produced = false; std::vector<sb_mutation_row> rows; };
+   std::vector<SequenceRows> mutationRowsAll(const EvaluatedFilters& filters, const std::vector<std::string>& names, int alphabet_id, double min_proportion) const {
+      std::vector<SequenceRows> out(names.size());
+      auto one = [&](size_t k) { out[k].produced = mutationRows(filters, names[k], alphabet_id, min_proportion, out[k].rows); };
+      if (names.size() <= 1) { for (size_t k = 0; k < names.size(); ++k) one(k); return out; }
+      {
+         std::lock_guard<std::mutex> lock(pool_mutex_);
+         if (!pool_) pool_ = std::make_unique<WorkerPool>(6);
+      }
+      pool_->run(names.size(), one);
+      return out;
+   }
    void mutationRowsFromTable(const std::string& name, int alphabet_id, const void* device_counts, double min_proportion, std::vector<sb_mutation_row>& rows) const {
       const auto& valid = alphabetById(alphabet_id).valid_mutation_symbols;
       size_t n = 0;
@@ -286,10 +371,13 @@ class DeviceDatabase {
          const int alphabet_id = query.action.alphabetId();
          QueryResult result;
          std::vector<uint32_t> counts;
-         std::vector<sb_mutation_row> rows;
-         for (const auto& name : mutationSequenceNames(query.action)) {   // mutations.cpp:258-270
-            if (!mutationRows(filters, name, alphabet_id, query.action.min_proportion, rows)) continue;
-            trace.lap("counts+select");
+         const std::vector<std::string> names = mutationSequenceNames(query.action);   // mutations.cpp:258-270
+         const std::vector<SequenceRows> all_rows = mutationRowsAll(filters, names, alphabet_id, query.action.min_proportion);
+         trace.lap("counts+select");
+         for (size_t k = 0; k < names.size(); ++k) {
+            if (!all_rows[k].produced) continue;
+            const std::string& name = names[k];
+            const std::vector<sb_mutation_row>& rows = all_rows[k].rows;
             addRowsToOutput(name, alphabetById(alphabet_id), db.getReferences(alphabet_id).at(name), rows, result.query_result);
             trace.lap("rows");
             if (tables && mutationCounts(filters, name, alphabet_id, counts)) (*tables)[name] = counts;   // the whole table, for the parity tests
@@ -313,12 +401,15 @@ class DeviceDatabase {
       const int alphabet_id = action.alphabetId();
       const Alphabet& alphabet = alphabetById(alphabet_id);
       std::string out = "{\"queryResult\":[";
-      std::vector<sb_mutation_row> rows;
       bool first = true;
       char number[16];
-      for (const auto& name : mutationSequenceNames(action)) {
-         if (!mutationRows(filters, name, alphabet_id, action.min_proportion, rows)) continue;
-         trace.lap("counts+select");
+      const std::vector<std::string> names = mutationSequenceNames(action);
+      const std::vector<SequenceRows> all_rows = mutationRowsAll(filters, names, alphabet_id, action.min_proportion);
+      trace.lap("counts+select");
+      for (size_t k = 0; k < names.size(); ++k) {
+         if (!all_rows[k].produced) continue;
+         const std::string& name = names[k];
+         const std::vector<sb_mutation_row>& rows = all_rows[k].rows;
          const auto& reference = db.getReferences(alphabet_id).at(name);
          std::string quoted_name;
          json::Value::writeString(quoted_name, name);
@@ -345,6 +436,9 @@ class DeviceDatabase {
    }
 
   private:
+   mutable std::mutex pool_mutex_;
+   mutable std::unique_ptr<WorkerPool> pool_;
+
    struct StoreRange { const Bitmap* begin; const Bitmap* end; uint32_t store_id; uint32_t sigma; };
    std::vector<StoreRange> store_ranges;
    std::unordered_map<const SequenceStorePartition*, uint32_t> store_ids;
