@@ -195,24 +195,25 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    if world > 1:      # the library sums the count tables over the ranks itself (ncclReduce to rank 0 on the stream of the count kernels)
+        id_t = torch.zeros(128, dtype=torch.uint8, device=counts.device)
+        if rank == 0:
+            id_t.copy_(torch.frombuffer(bytearray(pysilo.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(id_t, 0)
+        pysilo.comm_init(engine, bytes(id_t.cpu().numpy().tobytes()), rank, world)
+
     def device_step():
-        prepared.run_device(0, counts.data_ptr(), table_len)      # synchronous on the library's stream
-        if world > 1:
-            dist.reduce(counts, dst=0, op=dist.ReduceOp.SUM)       # uint32 sums are the same bits as int32 sums
-            torch.cuda.synchronize()
+        prepared.run_device(0, counts.data_ptr(), table_len)      # synchronous; for N > 1 it ends with the NCCL reduce of the table to rank 0
 
     def e2e_step():
         if world == 1:
             return engine.execute_text(query_bytes)     # the JSON response text, as the reference's handler returns it
         q = pysilo.DistributedQuery(engine, query_json)
-        produced = torch.tensor([int(q.local_table_device(0, counts.data_ptr(), table_len))], dtype=torch.int32, device=counts.device)
-        dist.reduce(counts, dst=0, op=dist.ReduceOp.SUM)
-        dist.all_reduce(produced, op=dist.ReduceOp.MAX)
+        q.local_table_device(0, counts.data_ptr(), table_len)      # local filter + count table, NCCL reduce to rank 0
         result = None
         if rank == 0:
-            if int(produced.item()):
-                q.set_table_device(0, counts.data_ptr())          # rows are selected on the device; only they come back
-            result = q.finish()
+            q.set_table_device(0, counts.data_ptr())              # rows are selected on the device; only they come back
+            result = q.finish_text()                               # (a table of zeros -- no rank produced anything -- selects no row)
         q.close()
         return result
 
@@ -343,6 +344,7 @@ def main():
         print(json.dumps(line), flush=True)
     prepared.close()
     if world > 1:
+        pysilo.comm_free(engine)
         dist.barrier()
         dist.destroy_process_group()
 

@@ -133,7 +133,21 @@ int sb_result_free(sb_result* r);
  * preFilterBitmaps (mutations.cpp:36-63) which then yields no entry for the sequence. */
 int sb_mutations(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
                  sb_result* const* results, uint32_t* counts, size_t counts_len, int* produced);
-/* Same, but leaves the table in device memory (for an NCCL reduce over NVLink before the copy). */
+/* ---- multi-GPU: partitions are sharded over processes (one per GPU); the only exchange of the path is the sum of the
+ * count tables (the reference sums over partitions in mutations.cpp:71,108). The library issues it itself:
+ * one ncclReduce (uint32, sum, root rank 0) on the stream of the count kernels, so the exchange costs one launch.
+ * NCCL is loaded at run time (dlopen libnccl.so.2, or the file SB_NCCL_LIB names); single-GPU use never touches it. A
+ * process that also uses PyTorch imports torch first, so that the one libnccl.so.2 of the process is torch's.
+ *   sb_comm_unique_id   rank 0: a fresh ncclUniqueId (128 bytes) for the caller to hand to every rank
+ *   sb_comm_init        every rank: joins the communicator on the db's device. From then on sb_mutations_device leaves the
+ *                       SUM over all ranks in rank 0's buffer (other ranks: their local table), and every rank must call
+ *                       it for the same sequence in the same order (collective), one query at a time.
+ *   sb_comm_free        leaves the communicator (sb_db_free does it too). */
+int sb_comm_unique_id(void* id_128_bytes);
+int sb_comm_init(sb_db* db, const void* id_128_bytes, int rank, int world_size);
+int sb_comm_free(sb_db* db);
+
+/* Same, but leaves the table in device memory (for the reduce over NVLink before the copy; see sb_comm_init). */
 int sb_mutations_device(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions,
                         sb_result* const* results, void* device_counts, size_t counts_len, int* produced);
 /* The selection step of addMutationsToOutput (mutations.cpp:196-215) on the device, so that only the

@@ -2,6 +2,8 @@
 // this file holds the database object and the ingest / finalize entry points, api_filter.inc the
 // filter evaluation (replaces Operator::evaluate), api_action.inc the Mutations / Aggregated actions.
 #include <atomic>
+#include <dlfcn.h>
+#include <nccl.h>
 #include "common.cuh"
 #include "kernels_action.cuh"
 #include "kernels_stream.cuh"
@@ -91,8 +93,41 @@ struct sb_lane {
 };
 constexpr uint32_t SB_LANES = 8;
 
+namespace sb {
+// NCCL entry points, resolved at run time (the process may already hold torch's copy of libnccl.so.2: dlopen returns that one)
+struct NcclApi {
+   ncclResult_t (*getUniqueId)(ncclUniqueId*) = nullptr;
+   ncclResult_t (*commInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+   ncclResult_t (*reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+   ncclResult_t (*commDestroy)(ncclComm_t) = nullptr;
+   const char* (*getErrorString)(ncclResult_t) = nullptr;
+   static NcclApi& get() {
+      static NcclApi api = [] {
+         NcclApi a;
+         // SB_NCCL_LIB names another copy. A process that also imports PyTorch must import it first: the loader keeps one
+         // libnccl.so.2 per process, and torch needs its own (newer) one.
+         const char* path = getenv("SB_NCCL_LIB") ? getenv("SB_NCCL_LIB") : "libnccl.so.2";
+         void* lib = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+         if (!lib) throw Error(std::string(path) + " cannot be loaded: " + dlerror());
+         auto sym = [&](const char* name) { void* p = dlsym(lib, name); if (!p) throw Error(std::string("libnccl.so.2 lacks ") + name); return p; };
+         a.getUniqueId = reinterpret_cast<decltype(a.getUniqueId)>(sym("ncclGetUniqueId"));
+         a.commInitRank = reinterpret_cast<decltype(a.commInitRank)>(sym("ncclCommInitRank"));
+         a.reduce = reinterpret_cast<decltype(a.reduce)>(sym("ncclReduce"));
+         a.commDestroy = reinterpret_cast<decltype(a.commDestroy)>(sym("ncclCommDestroy"));
+         a.getErrorString = reinterpret_cast<decltype(a.getErrorString)>(sym("ncclGetErrorString"));
+         return a;
+      }();
+      return api;
+   }
+};
+#define SB_NCCL(call) do { ncclResult_t r__ = (call); if (r__ != ncclSuccess) throw ::sb::Error(std::string(#call) + " failed: " + ::sb::NcclApi::get().getErrorString(r__)); } while (0)
+}  // namespace sb
+
 struct sb_db {
    int device = 0, sm_count = 148;
+   ncclComm_t comm = nullptr;          // sb_comm_init: count tables are summed over the ranks (root 0)
+   int comm_rank = 0, comm_world = 1;
+   std::mutex comm_mutex;
    uint32_t n_partitions = 0;
    bool finalized = false;
    std::mutex mutex;
@@ -128,6 +163,7 @@ struct sb_db {
 
    ~sb_db() {
       cudaSetDevice(device);
+      if (comm) { sb::NcclApi::get().commDestroy(comm); comm = nullptr; }
       for (auto& c : columns) if (c.device) cudaFree(c.device);
       if (ev_timer_begin) { cudaEventDestroy(ev_timer_begin); cudaEventDestroy(ev_timer_end); }
       lanes.clear();
@@ -175,6 +211,39 @@ int sb_db_create(int device, uint32_t n_partitions, sb_db** out) {
       SB_CUDA(cudaEventCreate(&db->ev_timer_end));
       db->stats.n_partitions = n_partitions;
       *out = db.release();
+   });
+}
+
+int sb_comm_unique_id(void* id_128_bytes) {
+   return guarded([&] {
+      static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+      ncclUniqueId id;
+      SB_NCCL(NcclApi::get().getUniqueId(&id));
+      memcpy(id_128_bytes, &id, sizeof id);
+   });
+}
+
+int sb_comm_init(sb_db* db, const void* id_128_bytes, int rank, int world_size) {
+   return guarded([&] {
+      SB_REQUIRE(db && !db->comm, "sb_comm_init called twice");
+      SB_REQUIRE(world_size >= 1 && rank >= 0 && rank < world_size, "rank must be in [0, world_size)");
+      useDevice(db);
+      ncclUniqueId id;
+      memcpy(&id, id_128_bytes, sizeof id);
+      SB_NCCL(NcclApi::get().commInitRank(&db->comm, world_size, id, rank));
+      db->comm_rank = rank;
+      db->comm_world = world_size;
+   });
+}
+
+int sb_comm_free(sb_db* db) {
+   return guarded([&] {
+      if (!db || !db->comm) return;
+      useDevice(db);
+      cudaDeviceSynchronize();
+      SB_NCCL(NcclApi::get().commDestroy(db->comm));
+      db->comm = nullptr;
+      db->comm_world = 1;
    });
 }
 

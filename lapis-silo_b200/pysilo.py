@@ -284,6 +284,26 @@ def k1_accumulated(engine, reset=False):
     return ms.value, n.value
 
 
+def comm_unique_id():
+    """rank 0: a fresh ncclUniqueId (128 bytes) to hand to every rank (sb_comm_unique_id)"""
+    buf = ctypes.create_string_buffer(128)
+    _sb_check(_sb().sb_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init(engine, unique_id, rank, world):
+    """every rank: from now on sb_mutations_device leaves the sum of the count tables of all ranks on rank 0 (NCCL reduce on the library's stream)"""
+    lib = _sb()
+    lib.sb_comm_init.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_int]
+    _sb_check(lib.sb_comm_init(engine.sb, unique_id, rank, world))
+
+
+def comm_free(engine):
+    lib = _sb()
+    lib.sb_comm_free.argtypes = [ctypes.c_void_p]
+    _sb_check(lib.sb_comm_free(engine.sb))
+
+
 def set_overlap(engine, enabled):
     lib = _sb()
     lib.sb_set_overlap.argtypes = [ctypes.c_void_p, ctypes.c_int]
@@ -363,6 +383,10 @@ class DistributedQuery:
 
     def finish(self, reduced_count=0):
         return json.loads(_take_string(host().silo_query_finish(self.handle, reduced_count)))["queryResult"]
+
+    def finish_text(self, reduced_count=0):
+        """the response body, not parsed (what execute_text returns on one GPU)"""
+        return _take_string(host().silo_query_finish(self.handle, reduced_count))
 
     def close(self):
         if self.handle:

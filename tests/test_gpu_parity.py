@@ -284,3 +284,24 @@ def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch)
                     tables_equal(libs, db, engine, {"action": {"type": "AminoAcidMutations", "minProportion": 0.01}, "filterExpression": f}, sorted(GENE_LENGTH.items()), 25)
         finally:
             engine.close()
+
+
+def test_in_library_reduce_single_rank(libs, synth_small):
+    """sb_comm_init with a world of one rank: the NCCL reduce that ends sb_mutations_device must leave the table as it is
+    (the multi-rank sum is exercised by bench.py --gpus N and, on the CPU, by tests/test_distributed_cpu.py)"""
+    import torch      # before the library loads NCCL: the process keeps one libnccl.so.2, and torch needs its own
+    pysilo, oracle = libs
+    engine = pysilo.Engine(synth_small, 0)
+    try:
+        pysilo.comm_init(engine, pysilo.comm_unique_id(), 0, 1)
+        f = synthetic_filters(synth_small)[3]
+        q = {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f}
+        counts = torch.zeros(16 * 3000, dtype=torch.int32, device="cuda:0")
+        prepared = pysilo.Prepared(engine, q)
+        prepared.run_device(0, counts.data_ptr(), 16 * 3000)
+        want, _ = oracle.mutation_counts(synth_small, q, "main", 16 * 3000)
+        assert np.array_equal(counts.cpu().numpy().view(np.uint32), want)
+        prepared.close()
+        pysilo.comm_free(engine)
+    finally:
+        engine.close()
