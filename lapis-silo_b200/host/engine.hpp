@@ -26,7 +26,8 @@ namespace silo::engine {
 
 // A few host threads that run the per-sequence parts of one query side by side (AminoAcidMutations over all genes: twelve
 // independent count tables). Every thread is bound to a lane of the library (streams + scratch of its own), so the
-// kernels of different sequences overlap on the GPU. One batch at a time; the calling thread takes part.
+// kernels of different sequences overlap on the GPU. It also shares the per-partition compile + lower of a filter. One batch
+// at a time (a second query that arrives meanwhile does its work on its own thread); the calling thread takes part.
 class WorkerPool {
  public:
    explicit WorkerPool(unsigned n_threads) {
@@ -39,7 +40,11 @@ class WorkerPool {
    }
    // runs job(0) ... job(n - 1), returns when all are done; rethrows the first exception
    void run(size_t n, const std::function<void(size_t)>& job) {
-      std::lock_guard<std::mutex> one_batch(batch_mutex_);
+      std::unique_lock<std::mutex> one_batch(batch_mutex_, std::try_to_lock);
+      if (!one_batch.owns_lock()) {      // the pool is busy with another query's batch: this thread does its own work
+         for (size_t k = 0; k < n; ++k) job(k);
+         return;
+      }
       {
          std::lock_guard<std::mutex> lock(mutex_);
          job_ = &job; n_ = n; next_ = 0; left_ = n; error_ = nullptr;
@@ -244,34 +249,42 @@ class DeviceDatabase {
       ~EvaluatedFilters() { for (auto* r : results) if (r) sb_result_free(r); }
    };
 
-   EvaluatedFilters evaluateTrees(const std::vector<const operators::Operator*>& trees) const {
-      std::vector<Plan> plans(trees.size());
+   EvaluatedFilters evaluatePlans(const std::vector<Plan>& plans) const {
       std::vector<const sb_node*> plan_ptrs;
       std::vector<uint32_t> plan_sizes;
       EvaluatedFilters out;
       out.handle = handle;
-      for (uint32_t local = 0; local < trees.size(); ++local) {
-         lower(*trees[local], local, plans[local]);
+      for (uint32_t local = 0; local < plans.size(); ++local) {
          plan_ptrs.push_back(plans[local].nodes.data());
          plan_sizes.push_back(static_cast<uint32_t>(plans[local].nodes.size()));
          out.partitions.push_back(local);
       }
-      out.results.assign(trees.size(), nullptr);
-      if (!trees.empty()) check(sb_filter_eval_batch(handle, static_cast<uint32_t>(trees.size()), out.partitions.data(), plan_ptrs.data(), plan_sizes.data(), out.results.data()));
+      out.results.assign(plans.size(), nullptr);
+      if (!plans.empty()) check(sb_filter_eval_batch(handle, static_cast<uint32_t>(plans.size()), out.partitions.data(), plan_ptrs.data(), plan_sizes.data(), out.results.data()));
       return out;
+   }
+   EvaluatedFilters evaluateTrees(const std::vector<const operators::Operator*>& trees) const {
+      std::vector<Plan> plans(trees.size());
+      for (uint32_t local = 0; local < trees.size(); ++local) lower(*trees[local], local, plans[local]);
+      return evaluatePlans(plans);
    }
 
    EvaluatedFilters evaluateFilter(const filter::Expression& expression) const {
-      std::vector<operators::OperatorPtr> trees;
-      std::vector<const operators::Operator*> ptrs;
+      // compile + lower per partition (query_engine.cpp:41-46 does it one partition after the other; the partitions are
+      // independent, so with more than a few of them the worker pool shares the work); evaluation is one batched call
+      const size_t n = owned.size();
+      std::vector<operators::OperatorPtr> trees(n);
+      std::vector<Plan> plans(n);
       HostTrace trace;
-      for (uint32_t global : owned) {   // compile per partition (query_engine.cpp:41-46); evaluation is one batched call
-         trees.push_back(expression.compile(db, *db.partitions[global], filter::AmbiguityMode::NONE));
-         ptrs.push_back(trees.back().get());
-      }
-      trace.lap("compile");
-      auto out = evaluateTrees(ptrs);
-      trace.lap("lower+eval");
+      auto one = [&](size_t local) {
+         trees[local] = expression.compile(db, *db.partitions[owned[local]], filter::AmbiguityMode::NONE);
+         lower(*trees[local], static_cast<uint32_t>(local), plans[local]);
+      };
+      if (n >= 8) workers().run(n, one);
+      else for (size_t local = 0; local < n; ++local) one(local);
+      trace.lap("compile+lower");
+      auto out = evaluatePlans(plans);
+      trace.lap("eval");
       return out;
    }
 
@@ -318,11 +331,7 @@ class DeviceDatabase {
       std::vector<SequenceRows> out(names.size());
       auto one = [&](size_t k) { out[k].produced = mutationRows(filters, names[k], alphabet_id, min_proportion, out[k].rows); };
       if (names.size() <= 1) { for (size_t k = 0; k < names.size(); ++k) one(k); return out; }
-      {
-         std::lock_guard<std::mutex> lock(pool_mutex_);
-         if (!pool_) pool_ = std::make_unique<WorkerPool>(6);
-      }
-      pool_->run(names.size(), one);
+      workers().run(names.size(), one);
       return out;
    }
    void mutationRowsFromTable(const std::string& name, int alphabet_id, const void* device_counts, double min_proportion, std::vector<sb_mutation_row>& rows) const {
@@ -436,6 +445,11 @@ class DeviceDatabase {
    }
 
   private:
+   WorkerPool& workers() const {
+      std::lock_guard<std::mutex> lock(pool_mutex_);
+      if (!pool_) pool_ = std::make_unique<WorkerPool>(6);
+      return *pool_;
+   }
    mutable std::mutex pool_mutex_;
    mutable std::unique_ptr<WorkerPool> pool_;
 
