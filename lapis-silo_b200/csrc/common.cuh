@@ -132,6 +132,8 @@ struct SeqDev {
    const uint2* miss_iv;          // [start, end) position intervals
    const uint64_t* miss_row_base; // [P] index of the partition's first row_off entry
    const uint64_t* miss_iv_base;  // [P]
+   const uint32_t* miss_tile_bits;   // per partition [n_tiles][ceil(n_rows / 32)]: bit = the row misses some position of the tile
+   const uint64_t* miss_tile_base;   // [P] word offset of the partition's block
    uint32_t length, sigma, tile_positions, n_tiles, n_partitions, n_items, n_slabs;
 };
 

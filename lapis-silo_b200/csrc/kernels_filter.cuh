@@ -162,49 +162,82 @@ __global__ void leaf_registered(const RegContainer* __restrict__ containers, con
    scatterContainer(scratch + job.dst_off, job.dst_words, c.key, c.kind, c.size, pay, reinterpret_cast<const uint4*>(pay), lane);
 }
 
-// does the row's missing-symbol bitmap contain `value`?  grid.y = job. A thread owns BSEL_ROWS rows (256 apart, so that
-// every load stays coalesced) and walks their binary searches in lockstep: the kernel is a chain of dependent loads
-// per row, and four independent chains per thread hide four times as much of it.
-constexpr uint32_t BSEL_ROWS = 4;
+// Builds the coarse index of the missing-symbol intervals of one partition (load time): bit (tile, row) is set when
+// the row misses some position of the tile. Thread per row.
+__global__ void build_miss_tiles(const uint32_t* __restrict__ row_off, const uint2* __restrict__ iv, uint32_t n_rows, uint32_t tile_positions,
+                                 uint32_t* __restrict__ bits, uint32_t words_per_tile) {
+   const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+   if (row >= n_rows) return;
+   for (uint32_t j = row_off[row]; j < row_off[row + 1]; ++j) {
+      const uint2 r = iv[j];
+      if (r.x >= r.y) continue;
+      for (uint32_t t = r.x / tile_positions; t <= (r.y - 1) / tile_positions; ++t) atomicOr(bits + size_t(t) * words_per_tile + (row >> 5), 1u << (row & 31));
+   }
+}
+
+// does the row's missing-symbol bitmap contain `value`?  grid.y = job. A warp owns 1,024 consecutive rows (32 words of the
+// result). The coarse index (build_miss_tiles) names the rows that miss anything in value's tile -- a few percent; the
+// warp writes them into a list in shared memory and its lanes share them evenly, four at a time per lane, so that the
+// dependent loads of the interval search (sorted, disjoint intervals: binary search) are few rounds with many loads in flight.
+constexpr uint32_t BSEL_ROWS = 32;     // rows per thread
 __global__ void __launch_bounds__(256)
 leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict__ jobs, uint64_t* __restrict__ scratch) {
+   __shared__ uint32_t cand_rows[8][1024];
+   __shared__ uint32_t found_words[8][32];
    const BselJob job = jobs[blockIdx.y];
-   const uint32_t row0 = blockIdx.x * (256 * BSEL_ROWS) + threadIdx.x;
-   if (blockIdx.x * (256 * BSEL_ROWS) >= job.n_rows) return;
+   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
+   const uint32_t word = blockIdx.x * 256 + threadIdx.x, n_words = (job.n_rows + 31) / 32;
+   if (blockIdx.x * 256 + warp * 32 >= n_words) return;        // whole warp beyond the partition
    const SeqDev& s = seqs[job.seq];
-   const uint32_t* row_off = s.miss_row_off + s.miss_row_base[job.partition];
-   const uint2* iv = s.miss_iv + s.miss_iv_base[job.partition];
-   uint32_t lo[BSEL_ROWS], hi[BSEL_ROWS];
-   bool contains[BSEL_ROWS];
+   const uint32_t tile = job.value / s.tile_positions;
+   uint32_t candidates = 0;
+   if (word < n_words && tile < s.n_tiles) candidates = __ldg(s.miss_tile_bits + s.miss_tile_base[job.partition] + size_t(tile) * n_words + word);
+   // candidate rows of the warp -> list
+   const uint32_t mine = __popc(candidates);
+   uint32_t before = mine;
 #pragma unroll
-   for (uint32_t k = 0; k < BSEL_ROWS; ++k) {
-      const uint32_t row = row0 + k * 256;
-      lo[k] = hi[k] = 0;
-      contains[k] = false;
-      if (row < job.n_rows) { lo[k] = __ldg(row_off + row); hi[k] = __ldg(row_off + row + 1); }
-   }
-   bool any = true;
-   while (any) {   // intervals are sorted and disjoint
-      any = false;
-      uint2 r[BSEL_ROWS];
-      uint32_t mid[BSEL_ROWS];
+   for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, before, d); if (lane >= uint32_t(d)) before += t; }
+   const uint32_t total = __shfl_sync(0xFFFFFFFFu, before, 31);
+   before -= mine;
+   found_words[warp][lane] = 0;
+   for (uint32_t c = candidates, k = before; c; c &= c - 1u) cand_rows[warp][k++] = word * 32 + uint32_t(__ffs(int(c))) - 1u;
+   __syncwarp();
+   if (total) {
+      const uint32_t* row_off = s.miss_row_off + s.miss_row_base[job.partition];
+      const uint2* iv = s.miss_iv + s.miss_iv_base[job.partition];
+      // four candidates per lane at a time, their searches walked in lockstep: four independent chains of dependent loads
+      for (uint32_t k0 = lane; k0 < total; k0 += 128) {
+         uint32_t row[4], lo[4], hi[4];
 #pragma unroll
-      for (uint32_t k = 0; k < BSEL_ROWS; ++k) { mid[k] = (lo[k] + hi[k]) >> 1; if (lo[k] < hi[k]) r[k] = __ldg(iv + mid[k]); }
+         for (uint32_t q = 0; q < 4; ++q) {
+            lo[q] = hi[q] = 0; row[q] = 0;
+            if (k0 + q * 32 < total) { row[q] = cand_rows[warp][k0 + q * 32]; lo[q] = __ldg(row_off + row[q]); hi[q] = __ldg(row_off + row[q] + 1); }
+         }
+         bool any = true;
+         while (any) {
+            any = false;
+            uint2 r[4];
+            uint32_t mid[4];
 #pragma unroll
-      for (uint32_t k = 0; k < BSEL_ROWS; ++k) {
-         if (lo[k] < hi[k]) {
-            if (job.value < r[k].x) hi[k] = mid[k]; else if (job.value >= r[k].y) lo[k] = mid[k] + 1; else { contains[k] = true; hi[k] = lo[k]; }
-            any |= lo[k] < hi[k];
+            for (uint32_t q = 0; q < 4; ++q) { mid[q] = (lo[q] + hi[q]) >> 1; if (lo[q] < hi[q]) r[q] = __ldg(iv + mid[q]); }
+#pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+               if (lo[q] < hi[q]) {
+                  if (job.value < r[q].x) hi[q] = mid[q];
+                  else if (job.value >= r[q].y) lo[q] = mid[q] + 1;
+                  else { atomicOr(&found_words[warp][(row[q] >> 5) & 31u], 1u << (row[q] & 31)); hi[q] = lo[q]; }
+                  any |= lo[q] < hi[q];
+               }
+            }
          }
       }
+      __syncwarp();
    }
-#pragma unroll
-   for (uint32_t k = 0; k < BSEL_ROWS; ++k) {
-      const uint32_t row = row0 + k * 256;
-      const bool hit = row < job.n_rows && contains[k] == (job.contains != 0);
-      const uint32_t bits = __ballot_sync(0xFFFFFFFFu, hit);
-      if (laneId() == 0 && bits) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[row >> 5] = bits;
-   }
+   if (word >= n_words) return;
+   const uint32_t found = found_words[warp][lane];
+   const uint32_t valid = (word + 1) * 32 <= job.n_rows ? ~0u : (~0u >> (32 - (job.n_rows & 31)));
+   const uint32_t bits = (job.contains ? found : ~found) & valid;
+   if (bits) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[word] = bits;
 }
 
 template <typename T>

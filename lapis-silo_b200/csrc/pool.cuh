@@ -126,7 +126,8 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
-   DeviceBuffer<uint64_t> miss_row_base, miss_iv_base;
+   DeviceBuffer<uint64_t> miss_row_base, miss_iv_base, miss_tile_base;
+   DeviceBuffer<uint32_t> miss_tile_bits;
    DeviceBuffer<uint32_t> full_tables;   // [P][sigma * length]
    DeviceBuffer<uint8_t> reference;      // [length] symbols of the reference sequence (row selection)
    DeviceBuffer<uint32_t> row_area;      // [4] counter + selected rows
@@ -335,6 +336,28 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.miss_iv.upload(iv);
    seq.miss_row_base.upload(row_base);
    seq.miss_iv_base.upload(iv_base);
+   {  // coarse index of the missing-symbol intervals: per (partition, tile) the rows that miss some position of the tile.
+      // BitmapSelection(position) then searches the intervals of those rows only (a few percent of the partition).
+      std::vector<uint64_t> tile_base(n_partitions, 0);
+      std::vector<uint32_t> part_rows(n_partitions, 0);
+      uint64_t words = 0;
+      for (uint32_t p = 0; p < n_partitions; ++p) {
+         tile_base[p] = words;
+         if (seq.store_of_partition[p] < 0) continue;
+         part_rows[p] = stores[seq.store_of_partition[p]]->n_rows;
+         words += uint64_t(seq.n_tiles) * ((part_rows[p] + 31) / 32);
+      }
+      seq.miss_tile_base.upload(tile_base);
+      seq.miss_tile_bits.alloc(size_t(std::max<uint64_t>(words, 1)));
+      SB_CUDA(cudaMemset(seq.miss_tile_bits.ptr, 0, seq.miss_tile_bits.bytes()));
+      for (uint32_t p = 0; p < n_partitions; ++p) {
+         if (part_rows[p] == 0) continue;
+         build_miss_tiles<<<(part_rows[p] + 255) / 256, 256>>>(seq.miss_row_off.ptr + row_base[p], seq.miss_iv.ptr + iv_base[p], part_rows[p], tp,
+                                                             seq.miss_tile_bits.ptr + tile_base[p], (part_rows[p] + 31) / 32);
+      }
+      SB_CUDA(cudaDeviceSynchronize());
+      stats.missing_bytes += seq.miss_tile_bits.bytes();
+   }
    stats.directory_bytes += seq.large_entries.bytes() + seq.items.bytes() + seq.segs.bytes() + seq.slabs.bytes();
    stats.payload_bytes += seq.postings.bytes() + seq.large_pool.bytes();
    stats.n_work_items += items.size();
@@ -343,6 +366,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    d.postings = seq.postings.ptr; d.large_entries = seq.large_entries.ptr; d.items = seq.items.ptr; d.segs = seq.segs.ptr; d.slabs = seq.slabs.ptr; d.slab_begin = seq.slab_begin.ptr;
    d.large_pool = seq.large_pool.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
    d.miss_row_off = seq.miss_row_off.ptr; d.miss_iv = seq.miss_iv.ptr; d.miss_row_base = seq.miss_row_base.ptr; d.miss_iv_base = seq.miss_iv_base.ptr;
+   d.miss_tile_bits = seq.miss_tile_bits.ptr; d.miss_tile_base = seq.miss_tile_base.ptr;
    d.length = L; d.sigma = sigma; d.tile_positions = tp; d.n_tiles = seq.n_tiles; d.n_partitions = n_partitions;
    d.n_items = seq.n_items; d.n_slabs = n_slabs;
 }
