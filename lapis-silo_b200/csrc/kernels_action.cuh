@@ -285,16 +285,29 @@ k1_and_popcount(const SeqDev s, const PartQuery* __restrict__ pq, const K1Map ma
 constexpr int K2_THREADS = 1024;
 constexpr uint32_t K2_MAX_WINDOW = 49152;   // positions per shared-memory difference array (192 KB)
 
+// Row blocks of a partition: the work of a block is its filtered rows (three dependent scattered loads each) far more than
+// its rows, and the filter's density differs from partition to partition, so a partition gets blocks in proportion to
+// cost = rows / 16 + filtered rows out of a budget of about one wave (host and kernel evaluate the same formula).
+__host__ __device__ inline uint64_t k2Cost(uint32_t n_rows, uint32_t cardinality) { return uint64_t(n_rows) / 16 + cardinality; }
+__host__ __device__ inline uint32_t k2Blocks(uint32_t n_rows, uint32_t cardinality, uint64_t total_cost, uint32_t budget) {
+   const uint32_t share = 1u + uint32_t(k2Cost(n_rows, cardinality) * budget / (total_cost ? total_cost : 1));
+   const uint32_t cap = (n_rows + 4095u) / 4096u;      // no block under 4,096 rows: every block pays the scan + flush over the positions
+   return share < cap ? share : (cap ? cap : 1u);
+}
+
 // grid: (row blocks, listed partitions, position windows). `plist` = partitions to process; a block owns
-// `rows_per_block` rows of one partition (the host sizes it so that the grid is about one wave).
+// an equal share of the rows of one partition (k2Blocks of them; the grid is about one wave).
 __global__ void __launch_bounds__(K2_THREADS)
 k2_missing(const SeqDev s, const PartQuery* __restrict__ pq, const uint32_t* __restrict__ plist, uint32_t* __restrict__ acc,
-           uint32_t window, uint32_t rows_per_block) {
+           uint32_t window, uint64_t total_cost, uint32_t budget) {
    extern __shared__ int diff[];   // [window + 1]
    __shared__ int warp_sums[32];
    __shared__ uint32_t n_filtered_s;
    const uint32_t partition = plist[blockIdx.y];
    const PartQuery q = pq[partition];
+   const uint32_t n_blocks = k2Blocks(q.n_rows, q.cardinality, total_cost, budget);
+   if (blockIdx.x >= n_blocks) return;
+   const uint32_t rows_per_block = ((q.n_rows + n_blocks - 1) / n_blocks + 31u) & ~31u;
    const uint32_t row0 = blockIdx.x * rows_per_block;
    if (row0 >= q.n_rows) return;
    const uint32_t row1 = min(q.n_rows, row0 + rows_per_block);
