@@ -6,7 +6,8 @@ response JSON out) and, for single-sequence Mutations queries, device-resident a
 
 Per query: rows N, partitions P, pool bytes by container kind, algorithmic bytes of the query (Mutations), median / p99
 latency and queries/s end to end (>= 20 timed calls after 3 warm-ups), device-resident step time, result rows.
-Parity is the job of tests/ (the same query shapes at sizes the oracle finishes); C1 is also checked against the oracle here.
+Parity is the job of tests/ (the same query shapes at sizes the oracle finishes, C1 itself in test_config_c1_thousand_sequences);
+this tool only measures and never touches oracle/.
 """
 import argparse
 import json
@@ -17,7 +18,6 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT / "lapis-silo_b200"))
-sys.path.insert(0, str(ROOT / "tests"))
 sys.path.insert(0, str(ROOT))
 GOLDEN = ROOT / "tests" / "golden"
 
@@ -70,14 +70,12 @@ def main():
     import bench
     L = 29903
     if "C1" in only:       # the reference's own 1,000-sequence dataset, Mutations under date + lineage
-        import oracle_bind
         db = pysilo.Database.from_directory(GOLDEN / "exampleDataset1000Sequences")
         engine = pysilo.Engine(db, 0)
         q = {"action": {"type": "Mutations", "minProportion": 0.05},
              "filterExpression": {"type": "And", "children": [{"type": "DateBetween", "column": "date", "from": "2020-01-01", "to": "2021-12-31"},
                                                               {"type": "PangoLineage", "column": "pangoLineage", "value": "B.1", "includeSublineages": True}]}}
-        body = measure(pysilo, torch, engine, db, "C1", q, 1000, (0, 16 * L))
-        assert json.loads(body)["queryResult"] == oracle_bind.execute(db, q), "C1 differs from the oracle"
+        measure(pysilo, torch, engine, db, "C1", q, 1000, (0, 16 * L))
         engine.close()
     if "C2" in only:       # 1 M sequences, Aggregated under And[Or[...], ...] with metadata predicates
         db = pysilo.Database.synthetic(1_000_000, 0x51100002)
