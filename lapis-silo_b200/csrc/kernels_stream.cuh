@@ -3,7 +3,7 @@
 // k1_and_popcount (kernels_action.cuh) launches one CTA per work item; every CTA pays a start-up (item fetch, 32 KB
 // filter copy), a block barrier and a flush during which its warps do not stream: measured with the per-CTA timeline
 // (tools/k1_experiment.py) those phases are a third of the CTA time, and a read-only kernel with the same loads is
-// 1.4x faster (tools/membench.cu). Here a CTA owns a byte-balanced share of the query's work items, cut on the host into
+// 1.4x faster (tools/membench.cu). Here a CTA owns a cost-balanced share of the query's work items, cut on the host into
 // RUNS (consecutive items of one slab). Per run the filter slab is copied into shared memory once; after that the 32
 // warps never meet at a barrier:
 //   * units (posting chunks, bitset halves, array pieces) of all items of the run form one ticket sequence; a warp takes
@@ -14,7 +14,8 @@
 //     before it takes its next unit: read the part's counters into registers, zero them, and -- once the part is handed
 //     back, so that the table can go to item j + n_tables as early as possible -- apply the flipped / deleted-symbol
 //     arithmetic of mutations.cpp:85-95, 122-133 and emit coalesced REDs from the registers.
-// Same arithmetic, same layouts, same results as k1_and_popcount (tests run both).
+// Same arithmetic, same layouts, same results as k1_and_popcount (tests run both). Opt-in (SB_K1=stream): measured 1.6x
+// slower than k1_and_popcount so far (DESIGN.md 4 has the numbers and the reasons).
 #pragma once
 #include "kernels_action.cuh"
 
@@ -27,7 +28,7 @@ constexpr uint32_t KS_MAX_ITEMS = 256;   // items per run (the host cuts longer 
 #ifndef SB_KS_ITEM_COST
 #define SB_KS_ITEM_COST 6
 #endif
-constexpr uint32_t KS_ITEM_COST = SB_KS_ITEM_COST;   // cost of flushing an item's table, in units (for the byte-balanced shares of the CTAs)
+constexpr uint32_t KS_ITEM_COST = SB_KS_ITEM_COST;   // cost of flushing an item's table, in units (for the cost-balanced shares of the CTAs)
 
 struct KsRun { uint32_t item_begin, item_end; };     // items [begin, end) of one slab, at most KS_MAX_ITEMS
 struct KsMap {
