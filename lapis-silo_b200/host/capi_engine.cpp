@@ -247,4 +247,22 @@ int silo_prepared_run_device(void* prepared_, uint32_t name_index, void* device_
    });
 }
 
+// Test hook for the host worker pool (tests/test_host_cpu.py; no device involved): runs n_jobs jobs that add
+// their index + 1 to a sum, `rounds` batches in a row, on `n_threads` workers + the caller; job `throw_at` (if >= 0)
+// throws. Returns the sum of the last batch, or -1 when the exception came back out of run().
+int64_t silo_test_worker_pool(uint32_t n_threads, uint32_t n_jobs, uint32_t rounds, int32_t throw_at) {
+   engine::WorkerPool pool(n_threads);
+   std::atomic<int64_t> sum{0};
+   try {
+      for (uint32_t r = 0; r < rounds; ++r) {
+         sum = 0;
+         pool.run(n_jobs, [&](size_t k) {
+            if (throw_at >= 0 && k == static_cast<size_t>(throw_at)) throw std::runtime_error("job failed");
+            sum += static_cast<int64_t>(k) + 1;
+         });
+      }
+   } catch (const std::runtime_error&) { return -1; }
+   return sum.load();
+}
+
 }  // extern "C"

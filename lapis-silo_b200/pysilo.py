@@ -76,6 +76,7 @@ def host():
         "silo_synth_clade_mutation": (None, [vp, u32, pu32, ctypes.c_char_p]),
         "silo_synth_lineage_name": (cp, [vp, u32]),
         "silo_synth_verify_against_builder": (ctypes.c_int64, [vp]),
+        "silo_test_worker_pool": (ctypes.c_int64, [u32, u32, u32, ctypes.c_int32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

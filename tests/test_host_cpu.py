@@ -55,3 +55,13 @@ def test_oracle_fast_mode_equals_faithful_mode(libs, synth_small):
     assert np.array_equal(slow, fast)
     aa = {"action": {"type": "AminoAcidMutations", "minProportion": 0.02}, "filterExpression": {"type": "True"}}
     assert oracle.execute(synth_small, aa, faithful=True) == oracle.execute(synth_small, aa, faithful=False)
+
+
+def test_worker_pool_runs_every_job_and_propagates_errors(libs):
+    """the host pool that shares per-partition compile + lower and the per-sequence tables of a query (host/engine.hpp)"""
+    pysilo, _ = libs
+    h = pysilo.host()
+    for threads, jobs, rounds in ((6, 23, 50), (1, 1, 3), (3, 1000, 5), (6, 0, 2)):
+        assert h.silo_test_worker_pool(threads, jobs, rounds, -1) == jobs * (jobs + 1) // 2
+    assert h.silo_test_worker_pool(6, 23, 1, 7) == -1        # an exception inside a job comes back to the caller
+    assert h.silo_test_worker_pool(6, 23, 3, -1) == 276      # and the pool is usable again afterwards (a fresh pool here)
