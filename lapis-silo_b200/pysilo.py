@@ -77,6 +77,19 @@ def host():
         "silo_synth_lineage_name": (cp, [vp, u32]),
         "silo_synth_verify_against_builder": (ctypes.c_int64, [vp]),
         "silo_test_worker_pool": (ctypes.c_int64, [u32, u32, u32, ctypes.c_int32]),
+        "silo_literal_create": (vp, []),
+        "silo_literal_free": (None, [vp]),
+        "silo_literal_db": (vp, [vp]),
+        "silo_literal_add_sequence": (ctypes.c_int, [vp, ctypes.c_int, cp, cp]),
+        "silo_literal_add_partition": (ctypes.c_int, [vp, u32, pu32]),
+        "silo_literal_set_bitmap": (ctypes.c_int, [vp, u32, cp, u32, ctypes.c_char, vp, u64, ctypes.c_int]),
+        "silo_literal_set_flags": (ctypes.c_int, [vp, u32, cp, u32, ctypes.c_char, ctypes.c_char]),
+        "silo_literal_set_missing": (ctypes.c_int, [vp, u32, cp, u32, vp, u32, ctypes.c_int]),
+        "silo_literal_set_missing_bulk": (ctypes.c_int, [vp, u32, cp, u32, vp, vp, ctypes.c_int]),
+        "silo_literal_add_values": (ctypes.c_int, [vp, u32, cp, u32, ctypes.c_char, vp, u64, u64, u64]),
+        "silo_literal_flip_most_numerous": (ctypes.c_int, [vp, u32, cp, u32, u32, cp]),
+        "silo_literal_delete_most_numerous": (ctypes.c_int, [vp, u32, cp, u32, u32, cp]),
+        "silo_literal_get_bitmap": (ctypes.c_int, [vp, u32, cp, u32, ctypes.c_char, ctypes.POINTER(vp), ctypes.POINTER(sz), cp, cp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -178,6 +191,81 @@ class Database:
             host().silo_db_free(self.handle)
         self.handle = None
         self._owner = None
+
+
+class LiteralDatabase(Database):
+    """A Database built bitmap by bitmap (host/capi_literal.cpp): store states that no builder produces -- flipped symbols,
+    flipped + deleted at one position, run containers in high keys, exact cardinalities and row counts. Position writers
+    follow src/silo/storage/position.cpp:24-127."""
+
+    def __init__(self, sequences):
+        """sequences: {name: reference text} (nucleotide) or {name: (alphabet_id, reference text)}"""
+        self._lit = host().silo_literal_create()
+        for name, ref in sequences.items():
+            alphabet, text = ref if isinstance(ref, tuple) else (0, ref)
+            self._check(host().silo_literal_add_sequence(self._lit, alphabet, name.encode(), text.encode()))
+        super().__init__(host().silo_literal_db(self._lit))
+        self.owned = []
+
+    @staticmethod
+    def _check(rc):
+        if rc != 0:
+            raise _error()
+
+    @staticmethod
+    def _ids(ids):
+        a = np.ascontiguousarray(ids, dtype=np.uint32)
+        return a, a.ctypes.data
+
+    def add_partition(self, sequence_count):
+        index = ctypes.c_uint32()
+        self._check(host().silo_literal_add_partition(self._lit, sequence_count, ctypes.byref(index)))
+        self.owned.append(index.value)
+        return index.value
+
+    def set_bitmap(self, partition, name, pos, symbol, ids, run_optimize=True):
+        a, ptr = self._ids(ids)
+        self._check(host().silo_literal_set_bitmap(self._lit, partition, name.encode(), pos, symbol.encode(), ptr, a.size, int(run_optimize)))
+
+    def set_flags(self, partition, name, pos, flipped=None, deleted=None):
+        self._check(host().silo_literal_set_flags(self._lit, partition, name.encode(), pos, (flipped or "\0").encode(), (deleted or "\0").encode()))
+
+    def set_missing(self, partition, name, row, ranges, run_optimize=True):
+        a, ptr = self._ids(np.asarray(ranges, dtype=np.uint32).reshape(-1))
+        self._check(host().silo_literal_set_missing(self._lit, partition, name.encode(), row, ptr, a.size // 2, int(run_optimize)))
+
+    def set_missing_bulk(self, partition, name, range_off, ranges, run_optimize=True):
+        """rows 0 .. len(range_off) - 2: row r misses the [start, end) position ranges ranges[range_off[r]:range_off[r + 1]]"""
+        off = np.ascontiguousarray(range_off, dtype=np.uint64)
+        a, ptr = self._ids(np.asarray(ranges, dtype=np.uint32).reshape(-1))
+        self._check(host().silo_literal_set_missing_bulk(self._lit, partition, name.encode(), off.size - 1, off.ctypes.data, ptr, int(run_optimize)))
+
+    def add_values(self, partition, name, pos, symbol, ids, offset, interval):
+        a, ptr = self._ids(ids)
+        self._check(host().silo_literal_add_values(self._lit, partition, name.encode(), pos, symbol.encode(), ptr, a.size, offset, interval))
+
+    def flip_most_numerous(self, partition, name, pos, sequence_count):
+        out = ctypes.create_string_buffer(2)
+        self._check(host().silo_literal_flip_most_numerous(self._lit, partition, name.encode(), pos, sequence_count, out))
+        return out.raw[:1].decode() if out.raw[0] else None
+
+    def delete_most_numerous(self, partition, name, pos, sequence_count):
+        out = ctypes.create_string_buffer(2)
+        self._check(host().silo_literal_delete_most_numerous(self._lit, partition, name.encode(), pos, sequence_count, out))
+        return out.raw[:1].decode() if out.raw[0] else None
+
+    def get_bitmap(self, partition, name, pos, symbol):
+        """(ids, flipped symbol or None, deleted symbol or None)"""
+        ptr, n = ctypes.c_void_p(), ctypes.c_size_t()
+        f, d = ctypes.create_string_buffer(2), ctypes.create_string_buffer(2)
+        self._check(host().silo_literal_get_bitmap(self._lit, partition, name.encode(), pos, symbol.encode(), ctypes.byref(ptr), ctypes.byref(n), f, d))
+        return _take_ids(ptr, n.value).tolist(), (f.raw[:1].decode() if f.raw[0] else None), (d.raw[:1].decode() if d.raw[0] else None)
+
+    def close(self):
+        if self._lit:
+            host().silo_literal_free(self._lit)
+        self._lit = None
+        self.handle = None
 
 
 class Engine:

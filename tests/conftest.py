@@ -8,6 +8,7 @@ import pytest
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT / "lapis-silo_b200"))
 sys.path.insert(0, str(ROOT / "tests"))
+sys.path.insert(0, str(ROOT))
 GOLDEN = ROOT / "tests" / "golden"
 
 
@@ -50,7 +51,8 @@ def synth_small(libs):
 
 @pytest.fixture(scope="session")
 def synth_medium(libs):
-    """120,000 synthetic sequences, full genome: partitions span two 65,536-row container keys."""
+    """120,000 synthetic sequences, full genome, 23 partitions of at most ~10,000 rows: one container key, one slab, no bitset
+    container (several keys / slabs / bitsets: tests/test_gpu_fullsize.py and tests/test_gpu_literal.py)."""
     pysilo, _ = libs
     return pysilo.Database.synthetic(120000, 0x51100002)
 

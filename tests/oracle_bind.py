@@ -90,3 +90,13 @@ def time_query_subset(db, query, partitions, faithful=True, threads=0):
     if seconds < 0:
         raise _err()
     return seconds, rows.value
+
+
+def mutation_counts_subset(db, query, sequence_name, table_len, partitions, faithful=True, threads=0):
+    """the table of `query` restricted to `partitions` (the others count as empty filters)"""
+    arr = (ctypes.c_uint32 * max(len(partitions), 1))(*partitions)
+    out = np.zeros(table_len, dtype=np.uint32)
+    rc = lib().oracle_mutation_counts_subset(db.handle, json.dumps(query).encode(), sequence_name.encode(), int(faithful), threads, arr, len(partitions), out.ctypes.data, table_len)
+    if rc not in (0, 4):
+        raise _err()
+    return out, rc == 0

@@ -208,39 +208,6 @@ def test_size_independent_properties(libs, synth_medium, medium_engine):
     assert per_position.max() <= n_total and per_position[15000] > 0.9 * n_total
 
 
-def test_full_size_properties_10m(libs):
-    """BASELINE config C3 at its full size (10 M sequences x 29,903 nt): the oracle does not finish there in seconds, so the
-    size-independent properties of the domain are checked instead -- linearity over row sets, count conservation,
-    idempotence, and the device-side row selection against the host's M5 loop on the same table."""
-    pysilo, _ = libs
-    n = 10_000_000
-    db = pysilo.Database.synthetic(n, 0x51100002)
-    engine = pysilo.Engine(db, 0)
-    try:
-        clade = db.clade_mutations()
-        picks = [clade[(7 * k) % len(clade)] for k in range(10)]
-        f = {"type": "N-Of", "numberOfMatchers": 3, "matchExactly": False,
-             "children": [{"type": "NucleotideEquals", "position": p + 1, "symbol": s} for p, s in picks]}
-        q = lambda flt: {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": flt}
-        count = lambda flt: engine.execute({"action": {"type": "Aggregated"}, "filterExpression": flt})[0]["count"]
-        length = 16 * 29903
-        t_in, any_in = engine.mutation_counts(q(f), "main", length)
-        t_again, _ = engine.mutation_counts(q(f), "main", length)
-        assert any_in and np.array_equal(t_in, t_again)                                   # idempotence
-        t_out, _ = engine.mutation_counts(q({"type": "Not", "child": f}), "main", length)
-        t_all, _ = engine.mutation_counts(q({"type": "True"}), "main", length)           # full partitions: the precomputed tables
-        assert np.array_equal(t_all, t_in + t_out)                                        # linearity over row sets
-        n_in, n_out = count(f), count({"type": "Not", "child": f})
-        assert 0 < n_in < n and n_in + n_out == n == count({"type": "True"})             # count conservation
-        per_position = t_in.reshape(16, 29903).sum(axis=0, dtype=np.uint64)
-        assert per_position.max() <= n_in and per_position[15000] > 0.9 * n_in            # every filtered row counted at most once per position
-        rows = engine.execute(q(f))
-        assert len(rows) > 0 and rows == pysilo.rows_from_table(db, q(f), "main", t_in)   # device row selection == host M5 on the same table
-    finally:
-        engine.close()
-        db.close()
-
-
 def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
     """Eight host threads issue different queries at once (one library lane each): every result equals its sequential result."""
     import threading

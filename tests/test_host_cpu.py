@@ -57,6 +57,30 @@ def test_oracle_fast_mode_equals_faithful_mode(libs, synth_small):
     assert oracle.execute(synth_small, aa, faithful=True) == oracle.execute(synth_small, aa, faithful=False)
 
 
+def test_oracle_fast_mode_equals_faithful_mode_with_bitset_containers(libs):
+    """The same on a partition that holds bitset containers and two container keys: the largest partition (~83,000 rows) of a
+    1 M-row full-genome database (2,812 bitset containers in all), under a filter that keeps a few thousand of its rows so that
+    the reference's O(|F| x L) contains() loop (mutations.cpp:76-82) stays in seconds. Fast mode is the authority at 10-40 M rows."""
+    pysilo, oracle = libs
+    db = pysilo.Database.synthetic(1_000_000, 0x51100002)
+    try:
+        stats = db.info()["sequences"]["main"]
+        assert stats["numberOfBitsetContainers"] > 1000
+        p = max(range(db.n_partitions), key=db.partition_rows)
+        assert db.partition_rows(p) > 65536
+        f = {"type": "And", "children": [{"type": "IntBetween", "column": "age", "from": 30, "to": 32},
+                                         {"type": "Not", "child": {"type": "NucleotideEquals", "position": 12, "symbol": "N"}}]}
+        n_f = len(oracle.filter_ids(db, f, p))
+        assert 500 < n_f < 10000, n_f
+        query = {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f}
+        slow, ok1 = oracle.mutation_counts_subset(db, query, "main", 16 * 29903, [p], faithful=True)
+        fast, ok2 = oracle.mutation_counts_subset(db, query, "main", 16 * 29903, [p], faithful=False)
+        assert ok1 and ok2 and slow.sum() > 29903 * 0.9 * n_f
+        assert np.array_equal(slow, fast)
+    finally:
+        db.close()
+
+
 def test_worker_pool_runs_every_job_and_propagates_errors(libs):
     """the host pool that shares per-partition compile + lower and the per-sequence tables of a query (host/engine.hpp)"""
     pysilo, _ = libs
