@@ -77,6 +77,16 @@ int oracle_filter_ids(const void* db_, const char* filter_json, uint32_t partiti
    });
 }
 
+// |F_p| only (no id export): lets a test classify partitions as empty / partial / full under a filter
+int oracle_filter_cardinality(const void* db_, const char* filter_json, uint32_t partition, uint64_t* cardinality) {
+   return guarded([&] {
+      const auto& db = *static_cast<const silo::Database*>(db_);
+      auto expression = silo::filter::parseExpression(silo::json::parse(filter_json));
+      auto op = expression->compile(db, *db.partitions.at(partition), silo::filter::AmbiguityMode::NONE);
+      *cardinality = oracle::evaluate(*op).get().cardinality();
+   });
+}
+
 // Full uint32[Σ][L] count table of one sequence for a Mutations / AminoAcidMutations query.
 // Returns 4 if the sequence produced no table (every partition's filter empty): `out` is zeroed.
 int oracle_mutation_counts(const void* db_, const char* query_json, const char* sequence_name, int faithful, int threads, uint32_t* out, size_t out_len) {

@@ -24,6 +24,7 @@ def lib():
         o.oracle_execute_query.argtypes = [vp, cp, ctypes.c_int, ctypes.c_int]
         o.oracle_eval_optree.argtypes = [cp, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
         o.oracle_filter_ids.argtypes = [vp, cp, ctypes.c_uint32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
+        o.oracle_filter_cardinality.argtypes = [vp, cp, ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint64)]
         o.oracle_mutation_counts.argtypes = [vp, cp, cp, ctypes.c_int, ctypes.c_int, vp, ctypes.c_size_t]
         o.oracle_mutation_counts_subset.argtypes = [vp, cp, cp, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, vp, ctypes.c_size_t]
         o.oracle_time_query_subset.restype = ctypes.c_double
@@ -72,6 +73,13 @@ def filter_ids(db, filter_expression, partition):
     if lib().oracle_filter_ids(db.handle, json.dumps(filter_expression).encode(), partition, ctypes.byref(ptr), ctypes.byref(n)) != 0:
         raise _err()
     return _ids(ptr, n.value)
+
+
+def filter_cardinality(db, filter_expression, partition):
+    n = ctypes.c_uint64()
+    if lib().oracle_filter_cardinality(db.handle, json.dumps(filter_expression).encode(), partition, ctypes.byref(n)) != 0:
+        raise _err()
+    return n.value
 
 
 def mutation_counts(db, query, sequence_name, table_len, faithful=True, threads=0):

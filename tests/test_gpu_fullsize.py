@@ -129,15 +129,29 @@ def test_c5_lineage_partitions_40m(libs):
     db = pysilo.Database.synthetic(40_000_000, 0x51100005)
     engine = pysilo.Engine(db, 0)
     try:
-        clade = sorted(n for n in db.lineage_names() if n.count(".") == 2)[0]
-        lineage = {"type": "PangoLineage", "column": "pangoLineage", "value": clade, "includeSublineages": True}
-        cards = [len(oracle.filter_ids(db, lineage, p)) for p in range(db.n_partitions)]
         rows = [db.partition_rows(p) for p in range(db.n_partitions)]
-        full = [p for p in range(db.n_partitions) if cards[p] == rows[p] and rows[p]]
+        # a lineage (with sublineages) that fills some partitions, cuts through at least one and misses the rest: lineages are
+        # the partition key, so a parent lineage covers whole partitions and shares the partition of merged small lineages
+        names = sorted({".".join(n.split(".")[:k]) for n in db.lineage_names() for k in range(1, n.count(".") + 2)}, key=lambda n: (n.count("."), n))
+        lineage = cards = fallback = None
+        for name in names:
+            flt = {"type": "PangoLineage", "column": "pangoLineage", "value": name, "includeSublineages": True}
+            c = [oracle.filter_cardinality(db, flt, p) for p in range(db.n_partitions)]
+            kinds = {"full" if c[p] == rows[p] else "partial" if c[p] else "empty" for p in range(db.n_partitions) if rows[p]}
+            if kinds == {"full", "partial", "empty"}:
+                lineage, cards = flt, c
+                break
+            if kinds == {"partial", "empty"} and fallback is None:
+                fallback = (flt, c)
+        if lineage is None:
+            lineage, cards = fallback
+        whole = {"type": "PangoLineage", "column": "pangoLineage", "value": names[0], "includeSublineages": True}      # the root lineage: every partition full
+        assert all(oracle.filter_cardinality(db, whole, p) == rows[p] for p in range(db.n_partitions))
         partial = [p for p in range(db.n_partitions) if 0 < cards[p] < rows[p]]
         empty = [p for p in range(db.n_partitions) if cards[p] == 0]
-        assert full and partial and empty, (cards, rows)
-        for flt in (lineage, bench.c3_query(db)["filterExpression"]):
+        full = [p for p in range(db.n_partitions) if cards[p] == rows[p] and rows[p]]
+        assert partial and empty
+        for flt in (lineage, whole, bench.c3_query(db)["filterExpression"]):
             got, _ = engine.mutation_counts(mutations(flt), "main", 16 * L)
             want, _ = oracle.mutation_counts(db, mutations(flt), "main", 16 * L, faithful=False)
             assert_tables_equal(got, want, L, flt["type"])
@@ -145,12 +159,12 @@ def test_c5_lineage_partitions_40m(libs):
             assert engine.execute(mutations(flt)) == oracle.execute(db, mutations(flt), faithful=False)
         engine.close()
         engine = None
-        for p in (full[0], partial[0], empty[0]):
+        for p, flt in ((full[0] if full else 0, lineage if full else whole), (partial[0], lineage), (empty[0], lineage)):
             one = pysilo.Engine(db, 0, [p])
             try:
-                got, got_any = one.mutation_counts(mutations(lineage), "main", 16 * L)
-                want, want_any = oracle.mutation_counts_subset(db, mutations(lineage), "main", 16 * L, [p], faithful=False)
-                assert got_any == want_any == (cards[p] > 0)
+                got, got_any = one.mutation_counts(mutations(flt), "main", 16 * L)
+                want, want_any = oracle.mutation_counts_subset(db, mutations(flt), "main", 16 * L, [p], faithful=False)
+                assert got_any == want_any == (oracle.filter_cardinality(db, flt, p) > 0)
                 assert_tables_equal(got, want, L, ("partition", p))
             finally:
                 one.close()
