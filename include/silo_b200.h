@@ -11,9 +11,8 @@
  * text available from sb_last_error() (thread-local). A failure never aborts the process: the host
  * turns it into an exception -> HTTP 500 (src/silo_api/query_handler.cpp:47-73).
  *
- * Threading: calls on one sb_db are serialised internally (one CUDA stream per sb_db); create /
- * finalize / free are exclusive (the reference swaps databases under a unique lock,
- * src/silo_api/database_mutex.cpp:15-18).
+ * Threading: create / finalize / free are exclusive (the reference swaps databases under a unique lock,
+ * src/silo_api/database_mutex.cpp:15-18); query entry points may be called concurrently (see below).
  * There is no CPU fallback: every entry point needs a CUDA device and fails loudly without one.
  */
 #ifndef SILO_B200_H
@@ -167,6 +166,36 @@ int sb_mutations_rows(sb_db* db, const char* store_name, uint32_t n, const uint3
                       double min_proportion, const uint8_t* valid, uint32_t n_valid,
                       sb_mutation_row* rows, size_t capacity, size_t* n_rows, int* produced);
 
+/* ---- a whole query as ONE submission --------------------------------------------------------------
+ * QueryEngine::executeQuery (query_engine.cpp:30-68) evaluates the partitions' filters (:40-49) and then runs the action
+ * (:60). These entry points take both call sites together: the plans of all listed partitions, the sequences whose
+ * Mutations rows are wanted (n_sequences == 0: filters only, e.g. for Aggregated) and the parameters of the row selection
+ * (see sb_mutation_rows_from_table). The library enqueues filter evaluation, Mutations::preFilterBitmaps (on the device),
+ * the count kernels and the row selection without reading anything back in between and synchronises once.
+ * out[k] belongs to sequence_names[k]: the caller provides rows / capacity; n_rows may exceed capacity (then call again
+ * with a larger buffer); produced == 0 mirrors preFilterBitmaps yielding no entry for the sequence (mutations.cpp:36-63).
+ * cardinalities (optional) receives |F_p| per listed partition.
+ * With sb_comm_init active every rank calls with its own partitions, in the same order on all ranks (sb_comm_enter); the
+ * tables are summed over the ranks before the selection and only rank 0 receives rows. */
+typedef struct sb_sequence_rows { sb_mutation_row* rows; size_t capacity; size_t n_rows; int produced; int pad; } sb_sequence_rows;
+int sb_query_mutations(sb_db* db, uint32_t n, const uint32_t* partitions, const sb_node* const* plans, const uint32_t* n_nodes,
+                       uint32_t n_sequences, const char* const* sequence_names, double min_proportion, const uint8_t* valid, uint32_t n_valid,
+                       sb_sequence_rows* out, uint64_t* cardinalities);
+/* The same query kept for replay: plans lowered and resident on the device, leaf bitmaps located once (a compiled Operator
+ * tree holds its bitmap pointers the same way, index_scan.h:18), buffers of its own. use_graph != 0 captures the launches
+ * in a CUDA graph: sb_query_run is then one graph launch + one synchronisation. One run at a time per sb_query; different
+ * sb_query objects run concurrently. */
+typedef struct sb_query sb_query;
+int sb_query_prepare(sb_db* db, uint32_t n, const uint32_t* partitions, const sb_node* const* plans, const uint32_t* n_nodes,
+                     uint32_t n_sequences, const char* const* sequence_names, double min_proportion, const uint8_t* valid, uint32_t n_valid,
+                     int use_graph, sb_query** out);
+int sb_query_run(sb_query* q, sb_sequence_rows* out, uint64_t* cardinalities);
+/* the uint32[n_symbols][length] table of sequence `index` of the last run, in device memory (valid until the next run) */
+int sb_query_table_device(sb_query* q, uint32_t index, const void** device_counts, size_t* counts_len);
+int sb_query_free(sb_query* q);
+/* synchronous copy out of device memory the library handed out (sb_query_table_device) */
+int sb_copy_from_device(void* host, const void* device, size_t bytes);
+
 /* aggregateWithoutGrouping (aggregated.cpp:58-66): sum of cardinalities, uint32 wrap-around. */
 int sb_aggregated_count(sb_db* db, uint32_t n, sb_result* const* results, uint32_t* count);
 
@@ -193,11 +222,12 @@ int sb_timer_end(sb_db* db, float* elapsed_ms);
 int sb_launch_count(const sb_db* db, uint64_t* launches);
 /* Bytes moved by cudaMemcpyAsync on the db's stream so far (plans / PartQuery up, cardinalities / tables down). */
 int sb_transfer_bytes(const sb_db* db, uint64_t* h2d, uint64_t* d2h);
-/* Accumulated CUDA-event time of k1_and_popcount since the last call with reset != 0, and its launch count. */
-/* By default independent kernels of a query overlap on a second stream (the row-wise leaves beside the container
- * leaves; the missing-symbol kernel beside the container scan). enabled = 0 serialises them on one stream, which is
+/* By default independent kernels of a query overlap on a second stream (the row-wise leaves beside the leaf location;
+ * the missing-symbol kernel beside the container scan). enabled = 0 serialises them on one stream, which is
  * how bench.py times the container scan alone for its roofline line. */
 int sb_set_overlap(sb_db* db, int enabled);
+/* Accumulated CUDA-event time of the container scan (k1_scan) since the last call with reset != 0, and its launch count
+ * (one-shot entry points only: a graph replay records no events). */
 int sb_k1_accumulated(sb_db* db, int reset, double* total_ms, uint64_t* launches);
 
 #ifdef __cplusplus

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <chrono>
+#include <condition_variable>
 #include <cstdint>
 #include <cstdlib>
 #include <cstdio>
@@ -86,7 +87,7 @@ struct LargeEntry {
 };
 static_assert(sizeof(LargeEntry) == 16, "LargeEntry must be 16 bytes");
 
-struct WorkItem {            // one CTA of the Mutations scan: a weight-bounded part of one (tile, slab) segment
+struct WorkItem {            // one unit of the Mutations scan: a weight-bounded part of one (tile, slab) segment
    uint32_t tile;
    uint32_t slab;
    uint32_t post_begin, post_end;     // postings [begin, end), begin a multiple of 4
@@ -105,10 +106,11 @@ struct SegRec {              // (tile, slab) segment: where its postings and lar
    uint32_t large_start;
 };
 
-// Per-partition, per-query state the action kernels read.
+// Per-partition, per-query state the action kernels read. Written on the DEVICE (classify_partitions): a query is one
+// submission, the host never sees the filter cardinalities before the count kernels are enqueued.
 enum : uint32_t { PART_EMPTY = 0, PART_PARTIAL = 1, PART_FULL = 2 };
 struct PartQuery {
-   const uint32_t* filter32;   // dense filter bitset (padded to whole 65,536-row blocks)
+   const uint32_t* filter32;   // dense filter bitset (padded to whole 4-key slabs)
    const uint32_t* rank_local; // per 64-bit word: popcount of the preceding words of its 256-word block
    const uint32_t* rank_block; // per 256-word block: popcount of all preceding blocks
    uint32_t state;
@@ -116,12 +118,27 @@ struct PartQuery {
    uint32_t n_rows;
    uint32_t pad;
 };
+// What the host knows of a partition's filter result when it enqueues the action: where things are, not what they hold.
+struct PartInput {
+   const uint32_t* filter32;
+   const uint32_t* rank_local;
+   const uint32_t* rank_block;
+   const uint64_t* cardinality;   // device counter written by finish_filters
+   uint32_t partition;
+   uint32_t pad;
+};
+// Per-(query, sequence) header the classification leaves for the count kernels.
+struct ActionHead {
+   uint32_t n_partial, n_full, produced, n_selected;   // n_selected: work items of the partial partitions (compact_items)
+   uint32_t next_item, pad0;                           // hand-out counter of the container scan
+   uint64_t k2_total_cost;
+};
 
 // Device view of one logical sequence (all partitions of one store name on this GPU).
 struct SeqDev {
    const uint32_t* postings;
    const LargeEntry* large_entries;
-   const WorkItem* items;       // ordered by slab (hence partition), then tile
+   const WorkItem* items;       // heaviest first over all partitions (the scan hands them out in this order)
    const SegRec* segs;          // [n_tiles * n_slabs + 1]
    const SlabRec* slabs;        // [n_slabs]
    const uint32_t* slab_begin;  // [P + 1] first slab of each partition
@@ -134,6 +151,8 @@ struct SeqDev {
    const uint64_t* miss_iv_base;  // [P]
    const uint32_t* miss_tile_bits;   // per partition [n_tiles][ceil(n_rows / 32)]: bit = the row misses some position of the tile
    const uint64_t* miss_tile_base;   // [P] word offset of the partition's block
+   const uint32_t* part_rows;        // [P] sequence_count of the partition's store, 0 = the partition has no store of this sequence
+   const uint32_t* item_partition;   // [n_items] partition of items[i] (items are ordered heaviest first over the whole sequence)
    uint32_t length, sigma, tile_positions, n_tiles, n_partitions, n_items, n_slabs;
 };
 

@@ -1,14 +1,18 @@
-// Filter kernels (sm_100a). A compiled Operator tree is evaluated in two steps:
-//  (1) every leaf that is not a pure range is densified into a zeroed scratch bitset:
-//        leaf_position_bitmap  IndexScan of a stored (position, symbol) bitmap   index_scan.cpp:28-30
-//        leaf_registered       IndexScan of a registered index bitmap / uploaded BitmapProducer result
-//        leaf_bitmap_selection BitmapSelection over missing_symbol_bitmaps       bitmap_selection.cpp:33-52
-//        leaf_selection        CompareToValueSelection predicates                selection.cpp:92-109,144-164
-//  (2) interpret_plans runs the postfix program word-by-word (64 rows per thread) with a register /
-//      local-memory stack: Intersection (intersection.cpp:76-127), Union (union.cpp:35-45), Complement
-//      (complement.cpp:50-54), Threshold (threshold.cpp:64-138) as a thermometer-coded bit-sliced
-//      counter with the reference's band pruning, Full / Empty / RangeSelection as computed masks.
-//      It also emits the per-word rank tables the run-container path of the Mutations scan needs.
+// Filter kernels (sm_100a). A compiled Operator tree (postfix program) is evaluated per partition in ONE pass over its
+// leaves -- no leaf of a roaring bitmap is ever densified into global memory:
+//   locate_leaves          where the containers of an IndexScan'ed (position, symbol) bitmap lie in the posting layout
+//                          (index_scan.cpp:28-30 borrows the stored bitmap; here: a warp search per (leaf, slab))
+//   leaf_bitmap_selection  BitmapSelection over missing_symbol_bitmaps   bitmap_selection.cpp:33-52   (row-wise: dense scratch)
+//   leaf_selection         CompareToValueSelection predicates            selection.cpp:92-109,144-164 (row-wise: dense scratch)
+//   eval_plans             one CTA per (plan, 65,536-row container key): every thread owns four 64-bit words of the key and
+//                          all threads run the same postfix program. A leaf's container of that key is read straight from the
+//                          pool -- a bitset with coalesced 64-bit loads, an array / run / posting list through an 8 KB shared-
+//                          memory staging bitset -- and combined on an evaluation stack in shared memory (top of stack in
+//                          registers): Intersection (intersection.cpp:76-127), Union (union.cpp:35-45), Complement
+//                          (complement.cpp:50-54), Threshold (threshold.cpp:64-138) as a thermometer-coded bit-sliced counter
+//                          with the reference's band pruning, Full / Empty / RangeSelection as computed masks.
+//                          Emits the result bitset and the rank tables the run-container path of the Mutations scan needs.
+//   finish_filters         per plan: block totals -> exclusive prefix, cardinality
 #pragma once
 #include "common.cuh"
 
@@ -18,110 +22,58 @@ enum : uint32_t {
    P_ZERO = 0, P_RANGES = 1, P_LEAF = 2, P_NOT = 3, P_AND = 4, P_OR = 5, P_ANDNOT = 6,
    P_THR_INIT = 7, P_THR_ADD = 8, P_THR_FIN = 9, P_END = 10
 };
-constexpr int INTERP_THREADS = 256;   // == words per rank block
-constexpr int INTERP_STACK = 48;
+constexpr int EVAL_THREADS = 256;
+constexpr uint32_t EVAL_WORDS = 1024;                 // 64-bit words per CTA: one container key (65,536 rows)
+constexpr int EVAL_PER_THREAD = EVAL_WORDS / EVAL_THREADS;
+constexpr uint32_t RANK_BLOCK_WORDS = 256;            // words per rank block
+constexpr uint32_t EVAL_MAX_SMEM_LEVELS = 24;         // evaluation stack levels kept in shared memory (8 KB each); deeper trees use global memory
+constexpr uint32_t EVAL_MAX_LEVELS = 4096;
 
 struct PlanDesc {
    uint32_t prog_off, prog_len;   // into the program stream
    uint32_t n_words;              // 64-bit words that can hold a set bit (max(row_count, leaf universe))
    uint32_t n_words_padded;       // multiple of 4096 (whole 4-key slabs of 262,144 rows), zero beyond n_words
-   uint64_t out_off;              // 64-bit word offset of the result in the result slab
+   uint64_t out_off;              // 64-bit word offset of the result in the result area
    uint64_t rank_local_off;       // uint32 offset
    uint64_t rank_block_off;       // uint32 offset
    uint64_t* cardinality;         // device counter
    uint32_t leaf_off, n_leaves;   // the plan's slice of the leaf table (P_LEAF operands index it)
 };
-struct LeafRef { uint64_t off; uint32_t words; uint32_t pad; };   // dense scratch bitset of a leaf: word offset, length
 
-struct PosLeafJob { uint32_t seq, partition, slot, slab; uint64_t dst_off; uint32_t dst_words, pad2; };   // one per (leaf, slab)
+// A leaf of a plan: where its set bits come from.
+enum : uint32_t { LEAF_DENSE = 0, LEAF_POS = 1, LEAF_REG = 2, LEAF_UP = 3 };
+struct LeafDesc {
+   uint32_t kind;
+   uint32_t a;       // DENSE: words of the scratch bitset | POS: sequence index | REG / UP: first container record
+   uint32_t b;       // POS: slabs of the partition        | REG / UP: number of container records
+   uint32_t c;       // POS: slot' (symbol * tile_positions + position in tile)
+   uint64_t off;     // DENSE: word offset in the scratch area | POS: index of the leaf's first LeafLoc (one per slab)
+};
+static_assert(sizeof(LeafDesc) == 24, "LeafDesc must be 24 bytes");
+struct LeafLoc { uint32_t post_begin, post_end, large_begin, large_end; };   // of one (leaf, slab): its postings and large entries
+
+struct LocJob { uint32_t seq, tile, slot2, slab; };                          // one per (leaf, slab); result at locs[job index]
 struct RegContainer { uint64_t pay_off; uint32_t size; uint16_t key; uint8_t kind; uint8_t pad; };  // size: array card / #runs
-struct RegLeafJob { uint32_t container; uint32_t dst_words; uint64_t dst_off; };
 struct BselJob { uint32_t seq, partition, value, contains, n_rows, pad; uint64_t dst_off; };
 struct PredDev { const void* column; int32_t dtype, comparator; int32_t i32; uint32_t u32; double f64; };
 struct SelJob { uint32_t pred_begin, n_preds, n_rows, pad; uint64_t dst_off; };
 
-__device__ __forceinline__ void setBit(uint64_t* dst, uint32_t n_words, uint32_t bit) {
-   if ((bit >> 6) < n_words) atomicOr(reinterpret_cast<unsigned long long*>(dst + (bit >> 6)), 1ULL << (bit & 63));
-}
-// sets [a, b] (inclusive) with word-granular atomics; the warp's lanes split the words
-__device__ __forceinline__ void setRangeWarp(uint64_t* dst, uint32_t n_words, uint32_t a, uint32_t b, uint32_t lane) {
-   const uint32_t wa = a >> 6, wb = b >> 6;
-   for (uint32_t w = wa + lane; w <= wb; w += 32) {
-      if (w >= n_words) break;
-      uint64_t mask = ~0ULL;
-      if (w == wa) mask &= ~0ULL << (a & 63);
-      if (w == wb) mask &= ~0ULL >> (63 - (b & 63));
-      atomicOr(reinterpret_cast<unsigned long long*>(dst + w), mask);
-   }
-}
+__device__ __forceinline__ uint32_t laneIdF() { return threadIdx.x & 31; }
 
-__device__ __forceinline__ void scatterContainer(uint64_t* dst, uint32_t n_words, uint32_t key, uint32_t kind, uint32_t size,
-                                                 const uint16_t* pay, const uint4* bitset, uint32_t lane) {
-   const uint32_t base = key << 16;
-   if (kind == KIND_ARRAY) {
-      if ((reinterpret_cast<uintptr_t>(pay) & 15u) == 0) {   // 8 values per load, 4 loads per lane in flight
-         const uint4* pay4 = reinterpret_cast<const uint4*>(pay);
-         const uint32_t n4 = (size + 7) / 8;
-         for (uint32_t i0 = lane; i0 < n4; i0 += 128) {
-            uint4 x[4];
-#pragma unroll
-            for (uint32_t k = 0; k < 4; ++k) x[k] = i0 + k * 32 < n4 ? __ldg(pay4 + i0 + k * 32) : make_uint4(0, 0, 0, 0);
-#pragma unroll
-            for (uint32_t k = 0; k < 4; ++k) {
-               const uint32_t wv[4] = {x[k].x, x[k].y, x[k].z, x[k].w};
-#pragma unroll
-               for (uint32_t t = 0; t < 8; ++t) {
-                  if ((i0 + k * 32) * 8 + t < size) setBit(dst, n_words, base | ((wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu));
-               }
-            }
-         }
-      } else {
-         for (uint32_t i = lane; i < size; i += 32) setBit(dst, n_words, base | __ldg(pay + i));
-      }
-   } else if (kind == KIND_RUN) {
-      for (uint32_t r = 0; r < size; ++r) {
-         const uint32_t start = __ldg(pay + 2 * r), len1 = __ldg(pay + 2 * r + 1);
-         setRangeWarp(dst, n_words, base + start, base + start + len1, lane);
-      }
-   } else {
-      // a bitmap has one container per key and every leaf owns its scratch region: plain 128-bit copy
-      if ((key + 1u) * 1024u <= n_words) {
-         uint4* out = reinterpret_cast<uint4*>(dst + size_t(key) * 1024u);
-#pragma unroll
-         for (uint32_t half = 0; half < 2; ++half) {
-            uint4 x[8];
-#pragma unroll
-            for (uint32_t t = 0; t < 8; ++t) x[t] = __ldg(bitset + (half * 8 + t) * 32 + lane);
-#pragma unroll
-            for (uint32_t t = 0; t < 8; ++t) out[(half * 8 + t) * 32 + lane] = x[t];
-         }
-      } else {
-         const uint64_t* src = reinterpret_cast<const uint64_t*>(bitset);
-         for (uint32_t i = lane; i < 1024; i += 32) {
-            const uint32_t w = key * 1024u + i;
-            if (w < n_words) dst[w] = __ldg(src + i);
-         }
-      }
-   }
-}
-
-// one warp per (leaf, slab): finds the postings and large containers of slot' in the sorted segment and scatters them
-__global__ void leaf_position_bitmap(const SeqDev* __restrict__ seqs, const PosLeafJob* __restrict__ jobs, uint32_t n_jobs, uint64_t* __restrict__ scratch) {
-   const uint32_t job_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = laneId();
+// one warp per (leaf, slab): the postings and large entries of slot' in the sorted (tile, slab) segment
+__global__ void locate_leaves(const SeqDev* __restrict__ seqs, const LocJob* __restrict__ jobs, uint32_t n_jobs, LeafLoc* __restrict__ locs) {
+   const uint32_t job_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = laneIdF();
    if (job_id >= n_jobs) return;
-   const PosLeafJob job = jobs[job_id];
+   const LocJob job = jobs[job_id];
    const SeqDev& s = seqs[job.seq];
-   const uint32_t pos = job.slot / s.sigma, sym = job.slot - pos * s.sigma;
-   const uint32_t tile = pos / s.tile_positions, slot2 = sym * s.tile_positions + (pos - tile * s.tile_positions);
-   uint64_t* dst = scratch + job.dst_off;
-   const SegRec seg = s.segs[size_t(tile) * s.n_slabs + job.slab];
-   const SegRec next = s.segs[size_t(tile) * s.n_slabs + job.slab + 1];
-   const uint32_t key0 = s.slabs[job.slab].key0;
-   {  // postings: warp-wide 32-ary lower bound of slot2 << 18 (3 dependent loads for a 32 K segment), then the run of equal slots
-      const uint32_t target = slot2 << POSTING_ROW_BITS;
+   const SegRec seg = s.segs[size_t(job.tile) * s.n_slabs + job.slab];
+   const SegRec next = s.segs[size_t(job.tile) * s.n_slabs + job.slab + 1];
+   LeafLoc loc;
+   {  // postings: warp-wide 32-ary lower bound of slot' << 18 (3 dependent loads for a 32 K segment), then the run of equal slots
+      const uint32_t target = job.slot2 << POSTING_ROW_BITS;
       uint32_t lo = seg.post_start, hi = next.post_start;   // answer in [lo, hi]
       while (hi - lo > 32) {
-         const uint32_t step = (hi - lo + 31) / 32;           // probes at lo + k*step - 1 ... cover the range
+         const uint32_t step = (hi - lo + 31) / 32;
          const uint32_t at = min(lo + (lane + 1) * step, hi) - 1;
          const bool below = __ldg(s.postings + at) < target;   // monotone in lane
          const uint32_t n_below = __popc(__ballot_sync(0xFFFFFFFFu, below));
@@ -133,33 +85,24 @@ __global__ void leaf_position_bitmap(const SeqDev* __restrict__ seqs, const PosL
          const bool below = lo + lane < hi && __ldg(s.postings + lo + lane) < target;
          lo += __popc(__ballot_sync(0xFFFFFFFFu, below));
       }
-      for (uint32_t e = lo + lane; e < next.post_start; e += 32) {
-         const uint32_t p = __ldg(s.postings + e);
-         if ((p >> POSTING_ROW_BITS) != slot2) break;
-         setBit(dst, job.dst_words, (key0 << 16) + (p & POSTING_ROW_MASK));
+      // a slot holds at most SLAB_KEYS containers of at most FLAT_MAX postings in a slab
+      uint32_t n = 0;
+      for (uint32_t base = lo; base < next.post_start; base += 32) {
+         const bool same = base + lane < next.post_start && (__ldg(s.postings + base + lane) >> POSTING_ROW_BITS) == job.slot2;
+         const uint32_t m = __ballot_sync(0xFFFFFFFFu, same);
+         n += __popc(m);
+         if (m != 0xFFFFFFFFu) break;
       }
+      loc.post_begin = lo; loc.post_end = lo + n;
    }
    {  // large containers of the slot (few per segment: plain binary search)
       uint32_t lo = seg.large_start, hi = next.large_start;
-      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (s.large_entries[mid].slot() < slot2) lo = mid + 1; else hi = mid; }
-      for (uint32_t e = lo; e < next.large_start; ++e) {
-         const LargeEntry w = s.large_entries[e];
-         if (w.slot() != slot2) break;
-         const uint4* pay = s.large_pool + w.offset16;
-         scatterContainer(dst, job.dst_words, key0 + w.keyLocal(), w.kind(), w.size, reinterpret_cast<const uint16_t*>(pay), pay, lane);
-      }
+      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (s.large_entries[mid].slot() < job.slot2) lo = mid + 1; else hi = mid; }
+      uint32_t e = lo;
+      while (e < next.large_start && s.large_entries[e].slot() == job.slot2) ++e;
+      loc.large_begin = lo; loc.large_end = e;
    }
-}
-
-// one warp per container of a registered / uploaded bitmap
-__global__ void leaf_registered(const RegContainer* __restrict__ containers, const uint16_t* __restrict__ pool,
-                                const RegLeafJob* __restrict__ jobs, uint32_t n_jobs, uint64_t* __restrict__ scratch) {
-   const uint32_t job_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = laneId();
-   if (job_id >= n_jobs) return;
-   const RegLeafJob job = jobs[job_id];
-   const RegContainer c = containers[job.container];
-   const uint16_t* pay = pool + c.pay_off;
-   scatterContainer(scratch + job.dst_off, job.dst_words, c.key, c.kind, c.size, pay, reinterpret_cast<const uint4*>(pay), lane);
+   if (lane == 0) locs[job_id] = loc;
 }
 
 // Builds the coarse index of the missing-symbol intervals of one partition (load time): bit (tile, row) is set when
@@ -179,19 +122,22 @@ __global__ void build_miss_tiles(const uint32_t* __restrict__ row_off, const uin
 // result). The coarse index (build_miss_tiles) names the rows that miss anything in value's tile -- a few percent; the
 // warp writes them into a list in shared memory and its lanes share them evenly, four at a time per lane, so that the
 // dependent loads of the interval search (sorted, disjoint intervals: binary search) are few rounds with many loads in flight.
+// Every 32-bit word of the leaf's scratch bitset (an even number of them) is written: the scratch area is never zeroed.
 constexpr uint32_t BSEL_ROWS = 32;     // rows per thread
 __global__ void __launch_bounds__(256)
 leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict__ jobs, uint64_t* __restrict__ scratch) {
    __shared__ uint32_t cand_rows[8][1024];
    __shared__ uint32_t found_words[8][32];
    const BselJob job = jobs[blockIdx.y];
-   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
-   const uint32_t word = blockIdx.x * 256 + threadIdx.x, n_words = (job.n_rows + 31) / 32;
-   if (blockIdx.x * 256 + warp * 32 >= n_words) return;        // whole warp beyond the partition
+   const uint32_t lane = laneIdF(), warp = threadIdx.x >> 5;
+   const uint32_t word = blockIdx.x * 256 + threadIdx.x, n_words = (job.n_rows + 31) / 32, n_words_out = (n_words + 1u) & ~1u;
+   if (blockIdx.x * 256 + warp * 32 >= n_words_out) return;        // whole warp beyond the partition
    const SeqDev& s = seqs[job.seq];
    const uint32_t tile = job.value / s.tile_positions;
+   // the coarse index is laid out with the STORE's row count; a BitmapSelection over fewer rows reads the same words
+   const uint32_t index_words = (s.part_rows[job.partition] + 31) / 32;
    uint32_t candidates = 0;
-   if (word < n_words && tile < s.n_tiles) candidates = __ldg(s.miss_tile_bits + s.miss_tile_base[job.partition] + size_t(tile) * n_words + word);
+   if (word < n_words && tile < s.n_tiles) candidates = __ldg(s.miss_tile_bits + s.miss_tile_base[job.partition] + size_t(tile) * index_words + word);
    // candidate rows of the warp -> list
    const uint32_t mine = __popc(candidates);
    uint32_t before = mine;
@@ -233,11 +179,14 @@ leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict
       }
       __syncwarp();
    }
-   if (word >= n_words) return;
-   const uint32_t found = found_words[warp][lane];
-   const uint32_t valid = (word + 1) * 32 <= job.n_rows ? ~0u : (~0u >> (32 - (job.n_rows & 31)));
-   const uint32_t bits = (job.contains ? found : ~found) & valid;
-   if (bits) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[word] = bits;
+   if (word >= n_words_out) return;
+   uint32_t bits = 0;
+   if (word < n_words) {
+      const uint32_t found = found_words[warp][lane];
+      const uint32_t valid = (word + 1) * 32 <= job.n_rows ? ~0u : (~0u >> (32 - (job.n_rows & 31)));
+      bits = (job.contains ? found : ~found) & valid;
+   }
+   reinterpret_cast<uint32_t*>(scratch + job.dst_off)[word] = bits;
 }
 
 template <typename T>
@@ -252,10 +201,12 @@ __device__ __forceinline__ bool compareValues(int32_t comparator, T a, T b) {
    }
 }
 
-// thread per row: conjunction of column predicates.  grid.y = job
+// thread per row: conjunction of column predicates.  grid.y = job; every 32-bit word of the scratch bitset is written
 __global__ void leaf_selection(const SelJob* __restrict__ jobs, const PredDev* __restrict__ preds, uint64_t* __restrict__ scratch) {
    const SelJob job = jobs[blockIdx.y];
    const uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+   const uint32_t n_words_out = (((job.n_rows + 31) / 32) + 1u) & ~1u;
+   if ((row >> 5) >= n_words_out) return;
    bool hit = row < job.n_rows;
    for (uint32_t k = 0; hit && k < job.n_preds; ++k) {
       const PredDev p = preds[job.pred_begin + k];
@@ -264,7 +215,7 @@ __global__ void leaf_selection(const SelJob* __restrict__ jobs, const PredDev* _
       else hit = compareValues<uint32_t>(p.comparator, __ldg(static_cast<const uint32_t*>(p.column) + row), p.u32);
    }
    const uint32_t bits = __ballot_sync(0xFFFFFFFFu, hit);
-   if (laneId() == 0 && bits) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[row >> 5] = bits;
+   if (laneIdF() == 0) reinterpret_cast<uint32_t*>(scratch + job.dst_off)[row >> 5] = bits;
 }
 
 // mask of the bits of word `w` that lie in [a, b)
@@ -277,138 +228,258 @@ __device__ __forceinline__ uint64_t rangeMask(uint32_t w, uint32_t a, uint32_t b
    return m;
 }
 
-// grid: (ceil(max n_words_padded / 256), n_plans); each thread owns one 64-bit word of one plan.
-// The interpreter is a serial fetch-decode chain per thread, so memory latency is taken out of it: the program and
-// the plan's leaf table are staged in shared memory, and the thread's words of the leaves -- consumed strictly in
-// program order -- are fetched eight at a time into a register window (eight independent loads in flight).
-// The top of the evaluation stack lives in a register; deeper entries in local memory.
-constexpr uint32_t INTERP_PROG_SMEM = 2048;   // program words staged in shared memory (longer programs are read from global)
-constexpr uint32_t INTERP_LEAF_SMEM = 128;    // leaf table entries staged in shared memory
-__global__ void __launch_bounds__(INTERP_THREADS)
-interpret_plans(const PlanDesc* __restrict__ plans, const uint32_t* __restrict__ programs, const LeafRef* __restrict__ leaf_table,
-                const uint64_t* __restrict__ scratch, uint64_t* __restrict__ out, uint32_t* __restrict__ ranks) {
-   __shared__ uint32_t prog_s[INTERP_PROG_SMEM];
-   __shared__ LeafRef leaf_s[INTERP_LEAF_SMEM];
-   __shared__ int warp_sums[INTERP_THREADS / 32];
-   const PlanDesc plan = plans[blockIdx.y];
-   const uint32_t w = blockIdx.x * INTERP_THREADS + threadIdx.x;
-   if (blockIdx.x * INTERP_THREADS >= plan.n_words_padded) return;
-   uint64_t result = 0;
-   if (blockIdx.x * INTERP_THREADS < plan.n_words) {
-      const uint32_t* prog = programs + plan.prog_off;
-      const LeafRef* leaves = leaf_table + plan.leaf_off;
-      if (plan.prog_len <= INTERP_PROG_SMEM) {
-         for (uint32_t i = threadIdx.x; i < plan.prog_len; i += INTERP_THREADS) prog_s[i] = prog[i];
-         prog = prog_s;
-      }
-      if (plan.n_leaves <= INTERP_LEAF_SMEM) {
-         for (uint32_t i = threadIdx.x; i < plan.n_leaves; i += INTERP_THREADS) leaf_s[i] = leaves[i];
-         leaves = leaf_s;
-      }
-      __syncthreads();
-      uint64_t win[8];      // words of leaves [8 * batch, 8 * batch + 8)
+struct EvalArgs {
+   const PlanDesc* plans;
+   const uint32_t* programs;
+   const LeafDesc* leaves;
+   const LeafLoc* locs;
+   const SeqDev* seqs;
+   const RegContainer* reg_containers;   // registered index bitmaps of the database
+   const uint16_t* reg_pool;
+   const RegContainer* up_containers;    // bitmaps that came with the plan (BitmapProducer results, host-evaluated selections)
+   const uint16_t* up_pool;
+   const uint64_t* scratch;              // dense bitsets of the row-wise leaves
+   uint64_t* out;
+   uint32_t* ranks;
+   uint64_t* deep_stack;                 // evaluation stacks in global memory when the batch needs more levels than fit in shared memory
+   uint32_t levels;                      // stack levels below the top of stack that any plan of the batch needs
+};
+
+// sets bit v of the staging bitset (65,536 bits as 2,048 32-bit words)
+__device__ __forceinline__ void stageBit(uint32_t* staging, uint32_t v) { atomicOr(staging + (v >> 5), 1u << (v & 31)); }
+// sets [a, b] (inclusive, < 65,536); `part` of `parts` cooperating threads takes every parts-th word
+__device__ __forceinline__ void stageRange(uint32_t* staging, uint32_t a, uint32_t b, uint32_t part, uint32_t parts) {
+   const uint32_t wa = a >> 5, wb = b >> 5;
+   for (uint32_t w = wa + part; w <= wb; w += parts) {
+      uint32_t mask = ~0u;
+      if (w == wa) mask &= ~0u << (a & 31);
+      if (w == wb) mask &= ~0u >> (31 - (b & 31));
+      atomicOr(staging + w, mask);
+   }
+}
+
+// One roaring container -> staging (arrays, runs). All threads of the CTA call it with the same arguments.
+__device__ __forceinline__ void stageContainer(uint32_t* staging, uint32_t kind, uint32_t size, const uint16_t* pay) {
+   if (kind == KIND_ARRAY) {
+      if ((reinterpret_cast<uintptr_t>(pay) & 15u) == 0) {   // 8 values per load
+         const uint4* pay4 = reinterpret_cast<const uint4*>(pay);
+         const uint32_t n4 = (size + 7) / 8;
+         for (uint32_t i = threadIdx.x; i < n4; i += EVAL_THREADS) {
+            const uint4 x = __ldg(pay4 + i);
+            const uint32_t wv[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-      for (int k = 0; k < 8; ++k) win[k] = 0;
-      uint32_t next_leaf = 0;
-      uint64_t stack[INTERP_STACK];
-      uint64_t tos = 0;   // top of stack; stack[0 .. sp-2] below it
-      int sp = 0;
-      const uint32_t* pc = prog;
+            for (uint32_t t = 0; t < 8; ++t) if (i * 8 + t < size) stageBit(staging, (wv[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu);
+         }
+      } else {
+         for (uint32_t i = threadIdx.x; i < size; i += EVAL_THREADS) stageBit(staging, __ldg(pay + i));
+      }
+   } else {   // KIND_RUN: few long runs are split over the threads word by word, many runs go one per thread
+      if (size <= 8) {
+         for (uint32_t r = 0; r < size; ++r) { const uint32_t start = __ldg(pay + 2 * r), len1 = __ldg(pay + 2 * r + 1); stageRange(staging, start, start + len1, threadIdx.x, EVAL_THREADS); }
+      } else {
+         for (uint32_t r = threadIdx.x; r < size; r += EVAL_THREADS) { const uint32_t start = __ldg(pay + 2 * r), len1 = __ldg(pay + 2 * r + 1); stageRange(staging, start, start + len1, 0, 1); }
+      }
+   }
+}
+
+// grid: (ceil(max n_words_padded / 1024), n_plans). Thread t owns words t, t + 256, t + 512, t + 768 of the key.
+// Shared memory: [levels][1024] uint64 evaluation stack (GLOBAL_STACK: in global memory instead) + 8 KB staging bitset.
+template <bool GLOBAL_STACK>
+__global__ void __launch_bounds__(EVAL_THREADS)
+eval_plans(const EvalArgs a) {
+   extern __shared__ __align__(16) uint64_t eval_smem[];
+   __shared__ int warp_sums[EVAL_PER_THREAD][EVAL_THREADS / 32];
+   const PlanDesc plan = a.plans[blockIdx.y];
+   const uint32_t chunk = blockIdx.x, w_base = chunk * EVAL_WORDS, tid = threadIdx.x;
+   if (w_base >= plan.n_words_padded) return;
+   uint64_t tos[EVAL_PER_THREAD];
+#pragma unroll
+   for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
+   if (w_base < plan.n_words) {
+      uint64_t* stk = GLOBAL_STACK ? a.deep_stack + (size_t(blockIdx.y) * gridDim.x + chunk) * size_t(a.levels) * EVAL_WORDS : eval_smem;
+      uint32_t* staging = reinterpret_cast<uint32_t*>(GLOBAL_STACK ? eval_smem : eval_smem + size_t(a.levels) * EVAL_WORDS);
+      uint64_t* staging64 = reinterpret_cast<uint64_t*>(staging);
+#pragma unroll
+      for (int j = 0; j < EVAL_PER_THREAD; ++j) staging64[j * EVAL_THREADS + tid] = 0;     // invariant: all zero between leaves
+      __syncthreads();
+      const uint32_t* pc = a.programs + plan.prog_off;
       const uint32_t* end = pc + plan.prog_len;
-#define SB_PUSH(value) do { if (sp > 0) stack[sp - 1] = tos; tos = (value); ++sp; } while (0)
+      const LeafDesc* leaves = a.leaves + plan.leaf_off;
+      int sp = 0;      // entries on the stack: levels 0 .. sp-2 in `stk`, the top in `tos`
+#define SB_LEVEL(l, j) stk[size_t(l) * EVAL_WORDS + (j) * EVAL_THREADS + tid]
+#define SB_SPILL() do { if (sp > 0) { _Pragma("unroll") for (int j = 0; j < EVAL_PER_THREAD; ++j) SB_LEVEL(sp - 1, j) = tos[j]; } ++sp; } while (0)
       while (pc < end) {
-         const uint32_t op = *pc++;
+         const uint32_t op = __ldg(pc++);
          switch (op) {
-            case P_ZERO: SB_PUSH(0ULL); break;
+            case P_ZERO:
+               SB_SPILL();
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
+               break;
             case P_RANGES: {
-               const uint32_t n = *pc++;
-               uint64_t m = 0;
-               for (uint32_t k = 0; k < n; ++k) { m |= rangeMask(w, pc[0], pc[1]); pc += 2; }
-               SB_PUSH(m);
+               const uint32_t n = __ldg(pc++);
+               SB_SPILL();
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
+               for (uint32_t k = 0; k < n; ++k) {
+                  const uint32_t r0 = __ldg(pc), r1 = __ldg(pc + 1);
+                  pc += 2;
+#pragma unroll
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] |= rangeMask(w_base + j * EVAL_THREADS + tid, r0, r1);
+               }
                break;
             }
-            case P_LEAF: {   // operand = index in the leaf table = number of leaves consumed so far
-               ++pc;
-               const uint32_t k = next_leaf & 7u;
-               if (k == 0) {
+            case P_LEAF: {
+               const LeafDesc leaf = leaves[__ldg(pc++)];
+               SB_SPILL();
 #pragma unroll
-                  for (uint32_t q = 0; q < 8; ++q) {
-                     win[q] = 0;
-                     if (next_leaf + q < plan.n_leaves) { const LeafRef r = leaves[next_leaf + q]; if (w < r.words) win[q] = __ldg(scratch + r.off + w); }
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
+               if (leaf.kind == LEAF_DENSE) {
+                  const uint64_t* src = a.scratch + leaf.off;
+#pragma unroll
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) { const uint32_t w = w_base + j * EVAL_THREADS + tid; if (w < leaf.a) tos[j] = __ldg(src + w); }
+                  break;
+               }
+               const uint64_t* direct = nullptr;     // a bitset container of this key: read as it lies in the pool
+               bool staged = false;
+               if (leaf.kind == LEAF_POS) {
+                  const uint32_t slab_local = chunk / SLAB_KEYS, key_local = chunk % SLAB_KEYS;
+                  if (slab_local < leaf.b) {
+                     const SeqDev& s = a.seqs[leaf.a];
+                     const LeafLoc loc = a.locs[leaf.off + slab_local];
+                     for (uint32_t e = loc.large_begin; e < loc.large_end; ++e) {
+                        const LargeEntry le = s.large_entries[e];
+                        if (le.keyLocal() != key_local) continue;
+                        if (le.kind() == KIND_BITSET) { direct = reinterpret_cast<const uint64_t*>(s.large_pool + le.offset16); break; }
+                        stageContainer(staging, le.kind(), le.size, reinterpret_cast<const uint16_t*>(s.large_pool + le.offset16));
+                        staged = true;
+                     }
+                     if (!direct && loc.post_begin < loc.post_end) {
+                        for (uint32_t i = loc.post_begin + tid; i < loc.post_end; i += EVAL_THREADS) {
+                           const uint32_t p = __ldg(s.postings + i);
+                           if (((p >> 16) & (SLAB_KEYS - 1)) == key_local) stageBit(staging, p & 0xFFFFu);
+                        }
+                        staged = true;
+                     }
+                  }
+               } else {
+                  const RegContainer* containers = (leaf.kind == LEAF_REG ? a.reg_containers : a.up_containers) + leaf.a;
+                  const uint16_t* pool = leaf.kind == LEAF_REG ? a.reg_pool : a.up_pool;
+                  uint32_t lo = 0, hi = leaf.b;       // containers are sorted by key
+                  while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (containers[mid].key < chunk) lo = mid + 1; else hi = mid; }
+                  if (lo < leaf.b && containers[lo].key == chunk) {
+                     const RegContainer c = containers[lo];
+                     if (c.kind == KIND_BITSET) direct = reinterpret_cast<const uint64_t*>(pool + c.pay_off);
+                     else { stageContainer(staging, c.kind, c.size, pool + c.pay_off); staged = true; }
                   }
                }
-               uint64_t v;
-               switch (k) {
-                  case 0: v = win[0]; break; case 1: v = win[1]; break; case 2: v = win[2]; break; case 3: v = win[3]; break;
-                  case 4: v = win[4]; break; case 5: v = win[5]; break; case 6: v = win[6]; break; default: v = win[7]; break;
+               if (direct) {
+#pragma unroll
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = __ldg(direct + j * EVAL_THREADS + tid);
+               } else if (staged) {      // uniform over the CTA
+                  __syncthreads();
+#pragma unroll
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) { tos[j] = staging64[j * EVAL_THREADS + tid]; staging64[j * EVAL_THREADS + tid] = 0; }
+                  __syncthreads();
                }
-               ++next_leaf;
-               SB_PUSH(v);
                break;
             }
-            case P_NOT: { const uint32_t rc = *pc++; tos ^= rangeMask(w, 0, rc); break; }   // flip(0, row_count)
-            case P_AND: --sp; tos = stack[sp - 1] & tos; break;
-            case P_OR: --sp; tos = stack[sp - 1] | tos; break;
-            case P_ANDNOT: --sp; tos = stack[sp - 1] & ~tos; break;
-            case P_THR_INIT: { const uint32_t d = *pc++; for (uint32_t j = 0; j < d; ++j) SB_PUSH(0ULL); break; }
-            case P_THR_ADD: {   // threshold.cpp:92-129, one child; T[j] = rows matching >= j+1 children so far
-               const int d = int(pc[0]), i = int(pc[1]), n = int(pc[2]), k = int(pc[3]);
-               const uint32_t negated = pc[4], rc = pc[5];
-               pc += 6;
-               const uint64_t c = tos;
+            case P_NOT: {   // flip(0, row_count)
+               const uint32_t rc = __ldg(pc++);
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] ^= rangeMask(w_base + j * EVAL_THREADS + tid, 0, rc);
+               break;
+            }
+            case P_AND:
                --sp;
-               uint64_t* t = stack + sp - d;     // the d planes are all in memory while a child is evaluated
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = SB_LEVEL(sp - 1, j) & tos[j];
+               break;
+            case P_OR:
+               --sp;
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = SB_LEVEL(sp - 1, j) | tos[j];
+               break;
+            case P_ANDNOT:
+               --sp;
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = SB_LEVEL(sp - 1, j) & ~tos[j];
+               break;
+            case P_THR_INIT: {
+               const uint32_t d = __ldg(pc++);
+               for (uint32_t k = 0; k < d; ++k) {
+                  SB_SPILL();
+#pragma unroll
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
+               }
+               break;
+            }
+            case P_THR_ADD: {   // threshold.cpp:92-129, one child; plane j = rows matching >= j + 1 children so far
+               const int d = int(__ldg(pc)), i = int(__ldg(pc + 1)), n = int(__ldg(pc + 2)), k = int(__ldg(pc + 3));
+               const uint32_t negated = __ldg(pc + 4), rc = __ldg(pc + 5);
+               pc += 6;
+               --sp;                              // the child is in `tos`; the d planes are levels sp-d .. sp-1, all in `stk`
+               const int base = sp - d;
                const int lo = max(0, n - k + i - 1);
-               for (int j = min(d - 1, i); j > lo; --j) t[j] |= negated ? (t[j - 1] & ~c) : (t[j - 1] & c);
-               if (k - i > n - 1) t[0] |= negated ? (c ^ rangeMask(w, 0, rc)) : c;
-               tos = t[d - 1];
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) {
+                  const uint64_t c = tos[j];
+                  for (int q = min(d - 1, i); q > lo; --q) SB_LEVEL(base + q, j) |= negated ? (SB_LEVEL(base + q - 1, j) & ~c) : (SB_LEVEL(base + q - 1, j) & c);
+                  if (k - i > n - 1) SB_LEVEL(base, j) |= negated ? (c ^ rangeMask(w_base + j * EVAL_THREADS + tid, 0, rc)) : c;
+                  tos[j] = SB_LEVEL(base + d - 1, j);
+               }
                break;
             }
             case P_THR_FIN: {
-               const int d = int(pc[0]), n = int(pc[1]);
-               const uint32_t exact = pc[2];
+               const int d = int(__ldg(pc)), n = int(__ldg(pc + 1));
+               const uint32_t exact = __ldg(pc + 2);
                pc += 3;
-               stack[sp - 1] = tos;
-               const uint64_t* t = stack + sp - d;
-               const uint64_t r = exact ? (t[n - 1] & ~t[n]) : t[d - 1];
-               sp -= d;
-               ++sp;
-               tos = r;
+               const int base = sp - d;           // top plane in `tos`, the others in levels base .. sp-2
+#pragma unroll
+               for (int j = 0; j < EVAL_PER_THREAD; ++j) {
+                  if (exact) tos[j] = (n - 1 == d - 1 ? tos[j] : SB_LEVEL(base + n - 1, j)) & ~(n == d - 1 ? tos[j] : SB_LEVEL(base + n, j));
+               }
+               sp = base + 1;
                break;
             }
             default: pc = end; break;
          }
       }
-#undef SB_PUSH
-      if (w < plan.n_words) result = tos;
+#undef SB_LEVEL
+#undef SB_SPILL
+#pragma unroll
+      for (int j = 0; j < EVAL_PER_THREAD; ++j) if (w_base + j * EVAL_THREADS + tid >= plan.n_words) tos[j] = 0;
    }
-   out[plan.out_off + w] = result;
-   // rank tables: exclusive popcount prefix inside this 256-word block, and the block total
-   const int pc_w = __popcll(result);
-   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
-   int incl = pc_w;
+   // result, rank tables: exclusive popcount prefix inside every 256-word block (block j of the key = words j*256 + t), block totals
+   const uint32_t lane = laneIdF(), warp = tid >> 5;
+   int pc_w[EVAL_PER_THREAD], incl[EVAL_PER_THREAD];
 #pragma unroll
-   for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
-   __syncthreads();
-   if (lane == 31) warp_sums[warp] = incl;
-   __syncthreads();
-   int before = 0, total = 0;
+   for (int j = 0; j < EVAL_PER_THREAD; ++j) {
+      a.out[plan.out_off + w_base + j * EVAL_THREADS + tid] = tos[j];
+      pc_w[j] = __popcll(tos[j]);
+      incl[j] = pc_w[j];
 #pragma unroll
-   for (int k = 0; k < INTERP_THREADS / 32; ++k) { const int v = warp_sums[k]; if (k < int(warp)) before += v; total += v; }
-   ranks[plan.rank_local_off + w] = uint32_t(before + incl - pc_w);
-   if (threadIdx.x == 0) {
-      ranks[plan.rank_block_off + blockIdx.x] = uint32_t(total);
-      if (total) atomicAdd(reinterpret_cast<unsigned long long*>(plan.cardinality), static_cast<unsigned long long>(total));
+      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl[j], d); if (lane >= uint32_t(d)) incl[j] += t; }
+      if (lane == 31) warp_sums[j][warp] = incl[j];
+   }
+   __syncthreads();
+#pragma unroll
+   for (int j = 0; j < EVAL_PER_THREAD; ++j) {
+      int before = 0, total = 0;
+#pragma unroll
+      for (int k = 0; k < EVAL_THREADS / 32; ++k) { const int v = warp_sums[j][k]; if (k < int(warp)) before += v; total += v; }
+      a.ranks[plan.rank_local_off + w_base + j * EVAL_THREADS + tid] = uint32_t(before + incl[j] - pc_w[j]);
+      if (tid == 0) a.ranks[plan.rank_block_off + chunk * EVAL_PER_THREAD + j] = uint32_t(total);
    }
 }
 
-// one warp per plan: block totals -> exclusive prefix
-__global__ void rank_block_prefix(const PlanDesc* __restrict__ plans, uint32_t n_plans, uint32_t* __restrict__ ranks) {
-   const uint32_t plan_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = laneId();
+// one warp per plan: block totals -> exclusive prefix; the grand total is the cardinality
+__global__ void finish_filters(const PlanDesc* __restrict__ plans, uint32_t n_plans, uint32_t* __restrict__ ranks) {
+   const uint32_t plan_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = laneIdF();
    if (plan_id >= n_plans) return;
    const PlanDesc plan = plans[plan_id];
    uint32_t* blocks = ranks + plan.rank_block_off;
-   const uint32_t n_blocks = plan.n_words_padded / INTERP_THREADS;
+   const uint32_t n_blocks = plan.n_words_padded / RANK_BLOCK_WORDS;
    uint32_t carry = 0;
    for (uint32_t base = 0; base < n_blocks; base += 32) {
       const uint32_t i = base + lane;
@@ -419,6 +490,7 @@ __global__ void rank_block_prefix(const PlanDesc* __restrict__ plans, uint32_t n
       if (i < n_blocks) blocks[i] = carry + incl - v;
       carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
    }
+   if (lane == 0) *plan.cardinality = carry;
 }
 
 }  // namespace sb

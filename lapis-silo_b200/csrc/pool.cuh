@@ -9,7 +9,14 @@
 
 namespace sb {
 
-struct ParsedContainer { uint16_t key; uint8_t kind; uint32_t size; uint32_t card; const uint16_t* data; };  // size: array card / #runs / bitset card
+// A container inside a caller's portable buffer. The payload may sit at ANY byte offset (the run-flag bitset makes it odd for
+// many container counts): it is only ever read through memcpy.
+struct ParsedContainer {
+   uint16_t key; uint8_t kind; uint32_t size; uint32_t card;   // size: array card / #runs / bitset card
+   const uint8_t* bytes;
+   uint16_t u16(size_t k) const { uint16_t v; memcpy(&v, bytes + 2 * k, 2); return v; }
+   uint64_t u64(size_t k) const { uint64_t v; memcpy(&v, bytes + 8 * k, 8); return v; }
+};
 
 // Roaring::readSafe equivalent; calls f(ParsedContainer) for every container, ascending keys.
 template <typename F>
@@ -51,15 +58,15 @@ inline void parsePortable(const uint8_t* p, size_t len, F&& f) {
          pos += 2;
          need(4 * size_t(r));
          SB_REQUIRE(r > 0, "roaring portable: empty run container");
-         c.kind = KIND_RUN; c.size = r; c.data = reinterpret_cast<const uint16_t*>(p + pos);
+         c.kind = KIND_RUN; c.size = r; c.bytes = p + pos;
          pos += 4 * size_t(r);
       } else if (c.card <= 4096) {
          need(2 * size_t(c.card));
-         c.kind = KIND_ARRAY; c.size = c.card; c.data = reinterpret_cast<const uint16_t*>(p + pos);
+         c.kind = KIND_ARRAY; c.size = c.card; c.bytes = p + pos;
          pos += 2 * size_t(c.card);
       } else {
          need(8192);
-         c.kind = KIND_BITSET; c.size = c.card; c.data = reinterpret_cast<const uint16_t*>(p + pos);
+         c.kind = KIND_BITSET; c.size = c.card; c.bytes = p + pos;
          pos += 8192;
       }
       f(c);
@@ -67,6 +74,11 @@ inline void parsePortable(const uint8_t* p, size_t len, F&& f) {
 }
 
 inline uint32_t payloadU16(const ParsedContainer& c) { return c.kind == KIND_ARRAY ? c.size : c.kind == KIND_RUN ? 2 * c.size : 4096; }
+inline void appendPayload(std::vector<uint16_t>& dst, const ParsedContainer& c) {
+   const size_t at = dst.size(), n16 = payloadU16(c);
+   dst.resize(at + n16);
+   memcpy(dst.data() + at, c.bytes, n16 * 2);
+}
 
 struct TmpContainer { uint32_t slot; uint16_t key; uint8_t kind; uint32_t size; uint64_t pay; };
 
@@ -114,15 +126,10 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<WorkItem> items;
    DeviceBuffer<SegRec> segs;
    DeviceBuffer<SlabRec> slabs;
-   DeviceBuffer<uint32_t> slab_begin;
+   DeviceBuffer<uint32_t> slab_begin, part_rows, item_partition;
    DeviceBuffer<uint4> large_pool;
    std::vector<uint32_t> h_slab_begin;    // [P + 1]
-   std::vector<uint32_t> h_item_begin;    // [P + 1] work items of each partition
-   std::vector<uint32_t> h_item_weight;   // [n_items] bytes of postings + large payload
-   std::vector<uint64_t> h_item_prefix;   // [n_items + 1] running sum of the k1_stream cost of the items (units + KS_ITEM_COST each)
-   std::vector<uint32_t> h_slab_item_begin;   // [n_slabs + 1] items of each slab (items are ordered by slab, then tile)
-   std::vector<uint32_t> h_by_weight;     // [n_items] item indices, per partition heaviest first
-   std::vector<WorkItem> h_items;         // host copy of `items`
+   std::vector<uint32_t> h_part_rows;     // [P] sequence_count of the partition's store (0 = none)
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
@@ -136,7 +143,7 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    uint64_t n_postings = 0, n_large = 0;
 };
 
-struct RegisteredBitmap { uint32_t partition; uint32_t first_container, n_containers; uint32_t max_value; };
+struct RegisteredBitmap { uint32_t partition; uint32_t first_container, n_containers; uint32_t max_value; };   // containers in ascending key order
 
 struct Column { uint32_t partition; int dtype; uint32_t n; void* device = nullptr; };
 
@@ -256,37 +263,15 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
          SB_REQUIRE(postings.size() < 0xFFFFFFF0ull, "more than 2^32 postings in one sequence");
       }
    }
-   {  // order: slab (hence partition), then tile: a persistent CTA of k1_stream takes consecutive items of one slab and keeps
-      // the slab's filter in shared memory. k1_and_popcount (one CTA per item) wants every partition's items heaviest
-      // first instead: h_by_weight lists them that way (the block scheduler hands out CTAs in index order).
+   std::vector<uint32_t> item_partition(items.size());
+   {  // order: heaviest first over the whole sequence -- the scan's persistent CTAs take the selected items of a query in
+      // this order from a device counter (longest-processing-time hand-out)
       std::vector<uint32_t> order(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) order[k] = k;
-      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return items[a].slab < items[b].slab; });   // creation order is tile-major
+      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_weight[a] > item_weight[b]; });
       std::vector<WorkItem> sorted(items.size());
-      for (uint32_t k = 0; k < order.size(); ++k) sorted[k] = items[order[k]];
+      for (uint32_t k = 0; k < order.size(); ++k) { sorted[k] = items[order[k]]; item_partition[k] = sorted[k].partition; }
       items.swap(sorted);
-      seq.h_item_weight.resize(items.size());
-      seq.h_item_prefix.assign(items.size() + 1, 0);
-      for (uint32_t k = 0; k < order.size(); ++k) {
-         seq.h_item_weight[k] = uint32_t(std::min<uint64_t>(item_weight[order[k]], 0xFFFFFFFFull));
-         // cost of an item in k1_stream: its units (a 2 KB posting chunk and a 4 KB bitset half take a warp about equally long)
-         // plus the flush of its count table, which costs about as much as KS_ITEM_COST units whatever the item holds
-         const WorkItem& it = items[k];
-         const uint32_t n4 = (it.post_end - it.post_begin + 3u) >> 2;
-         const uint32_t units = 2u * (it.large_end - it.large_begin) + (n4 + 32u * K1_UNROLL - 1u) / (32u * K1_UNROLL);
-         seq.h_item_prefix[k + 1] = seq.h_item_prefix[k] + units + KS_ITEM_COST;
-      }
-      seq.h_item_begin.assign(n_partitions + 1, 0);
-      seq.h_slab_item_begin.assign(size_t(n_slabs) + 1, 0);
-      for (const WorkItem& it : items) { seq.h_item_begin[slabs[it.slab].partition + 1]++; seq.h_slab_item_begin[it.slab + 1]++; }
-      for (uint32_t p = 0; p < n_partitions; ++p) seq.h_item_begin[p + 1] += seq.h_item_begin[p];
-      for (uint32_t k = 0; k < n_slabs; ++k) seq.h_slab_item_begin[k + 1] += seq.h_slab_item_begin[k];
-      seq.h_by_weight.resize(items.size());
-      for (uint32_t k = 0; k < items.size(); ++k) seq.h_by_weight[k] = k;
-      for (uint32_t p = 0; p < n_partitions; ++p) {
-         std::stable_sort(seq.h_by_weight.begin() + seq.h_item_begin[p], seq.h_by_weight.begin() + seq.h_item_begin[p + 1],
-                          [&](uint32_t a, uint32_t b) { return seq.h_item_weight[a] > seq.h_item_weight[b]; });
-      }
    }
    while (postings.size() % 4) postings.push_back(filler);
    segs.back() = {uint32_t(postings.size()), uint32_t(large_entries.size())};
@@ -324,7 +309,10 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.postings.upload(postings);
    seq.large_entries.upload(large_entries);
    seq.items.upload(items);
-   seq.h_items = items;
+   seq.item_partition.upload(item_partition);
+   seq.h_part_rows.assign(n_partitions, 0);
+   for (uint32_t p = 0; p < n_partitions; ++p) if (seq.store_of_partition[p] >= 0) seq.h_part_rows[p] = stores[seq.store_of_partition[p]]->n_rows;
+   seq.part_rows.upload(seq.h_part_rows);
    seq.segs.upload(segs);
    seq.slabs.upload(slabs);
    seq.slab_begin.upload(seq.h_slab_begin);
@@ -367,6 +355,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    d.large_pool = seq.large_pool.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
    d.miss_row_off = seq.miss_row_off.ptr; d.miss_iv = seq.miss_iv.ptr; d.miss_row_base = seq.miss_row_base.ptr; d.miss_iv_base = seq.miss_iv_base.ptr;
    d.miss_tile_bits = seq.miss_tile_bits.ptr; d.miss_tile_base = seq.miss_tile_base.ptr;
+   d.part_rows = seq.part_rows.ptr; d.item_partition = seq.item_partition.ptr;
    d.length = L; d.sigma = sigma; d.tile_positions = tp; d.n_tiles = seq.n_tiles; d.n_partitions = n_partitions;
    d.n_items = seq.n_items; d.n_slabs = n_slabs;
 }

@@ -1,12 +1,12 @@
 // libsilo_b200.so — C ABI (include/silo_b200.h) over the sm_100a kernels. One translation unit:
-// this file holds the database object and the ingest / finalize entry points, api_filter.inc the
-// filter evaluation (replaces Operator::evaluate), api_action.inc the Mutations / Aggregated actions.
+// this file holds the database object and the ingest entry points, pipeline.inc the lowering of plans and the launch
+// sequences of a query, api_filter.inc the filter evaluation (replaces Operator::evaluate), api_action.inc finalize + the
+// Mutations / Aggregated actions on evaluated filters, api_query.inc whole queries as one submission (and as CUDA graphs).
 #include <atomic>
 #include <dlfcn.h>
 #include <nccl.h>
 #include "common.cuh"
 #include "kernels_action.cuh"
-#include "kernels_stream.cuh"
 #include "kernels_filter.cuh"
 #include "pool.cuh"
 
@@ -27,15 +27,20 @@ struct PinnedBuffer {   // growable page-locked staging buffer
       return ptr;
    }
 };
+// growable device buffer, allocated and released in stream order (no device-wide synchronisation on the query path)
 struct GrowDevice {
    uint8_t* ptr = nullptr;
    size_t capacity = 0;
+   GrowDevice() = default;
+   GrowDevice(const GrowDevice&) = delete;
+   GrowDevice& operator=(const GrowDevice&) = delete;
    ~GrowDevice() { if (ptr) cudaFree(ptr); }
-   uint8_t* ensure(size_t n) {
+   uint8_t* ensure(size_t n, cudaStream_t stream) {
       if (n > capacity) {
-         if (ptr) cudaFree(ptr);
-         capacity = std::max<size_t>(n * 2, 1 << 16);
-         SB_CUDA(cudaMalloc(reinterpret_cast<void**>(&ptr), capacity));
+         if (ptr) SB_CUDA(cudaFreeAsync(ptr, stream));
+         ptr = nullptr;
+         capacity = std::max<size_t>(n + n / 2, 1 << 16);
+         SB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&ptr), capacity, stream));
       }
       return ptr;
    }
@@ -50,6 +55,14 @@ struct Slab {
    ~Slab() { if (ptr) { cudaSetDevice(device); cudaFreeAsync(ptr, stream); } }
 };
 
+// Everything one query in flight needs besides the index: the lowered plans, the filter results, the scratch of the row-wise
+// leaves, the per-sequence action state, the count tables, the selected rows, and the pinned images the copies go through.
+// A lane owns one (one-shot queries); a prepared query owns its own (fixed addresses: its launches are a CUDA graph).
+struct QueryBuffers {
+   GrowDevice blob, results, scratch, locs, deep_stack, action, tables, rows;
+   PinnedBuffer staging, out_host;
+};
+
 }  // namespace sb
 
 struct sb_result {
@@ -59,34 +72,27 @@ struct sb_result {
    const uint64_t* words;
    const uint32_t* rank_local;
    const uint32_t* rank_block;
+   const uint64_t* d_cardinality;   // the device counter finish_filters wrote (classification reads it on the device)
    uint64_t cardinality;
 };
 
-// One query in flight = one lane: its own streams, events and scratch buffers. A calling thread is bound to a lane
+// One query in flight = one lane: its own streams, events and buffers. A calling thread is bound to a lane
 // (round robin); calls of different threads overlap on the GPU, calls on one lane are serialised by its mutex.
 struct sb_lane {
    std::mutex mutex;
    cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: kernels independent of the main chain (fork / join through events)
-   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr;
+   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr, ev_begin = nullptr, ev_k1_begin = nullptr, ev_k1_end = nullptr, ev_end = nullptr;
    bool timing_valid = false, k1_ran = false;
    uint32_t last_launches = 0;
-   PinnedBuffer staging, counts_host, list_staging;
-   GrowDevice blob, scratch, action_scratch, table_scratch, k2_acc, row_area;
-   // the K1 work list of a sequence that is on the device: built for these partial partitions (rebuilt when they change)
-   struct K1List { GrowDevice device; bool valid = false, stream = false; std::vector<uint32_t> partial; uint32_t grid = 0; };
-   std::map<const void*, K1List> k1_lists;
+   QueryBuffers buffers;
    void create() {
       SB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
       SB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
-      SB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-      SB_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
-      SB_CUDA(cudaEventCreate(&ev_begin));
-      SB_CUDA(cudaEventCreate(&ev_k1_begin));
-      SB_CUDA(cudaEventCreate(&ev_k1_end));
-      SB_CUDA(cudaEventCreate(&ev_end));
+      for (cudaEvent_t* e : {&ev_fork, &ev_join, &ev_fork2, &ev_join2}) SB_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+      for (cudaEvent_t* e : {&ev_begin, &ev_k1_begin, &ev_k1_end, &ev_end}) SB_CUDA(cudaEventCreate(e));
    }
    ~sb_lane() {
-      if (ev_fork) { cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); cudaEventDestroy(ev_begin); cudaEventDestroy(ev_k1_begin); cudaEventDestroy(ev_k1_end); cudaEventDestroy(ev_end); }
+      for (cudaEvent_t e : {ev_fork, ev_join, ev_fork2, ev_join2, ev_begin, ev_k1_begin, ev_k1_end, ev_end}) if (e) cudaEventDestroy(e);
       if (stream2) cudaStreamDestroy(stream2);
       if (stream) cudaStreamDestroy(stream);
    }
@@ -140,12 +146,14 @@ struct sb_db {
    uint64_t k1_launches = 0;
    double k1_total_ms = 0;
    bool overlap = true;
-   uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of k1_stream (0 = one per SM)
+   uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of the container scan (0 = as many as are resident at once)
    uint32_t k1_pad_bytes = getenv("SB_K1_PAD_KB") ? uint32_t(atoi(getenv("SB_K1_PAD_KB"))) * 1024u : 0;   // experiments: extra dynamic shared memory per CTA (fewer CTAs per SM, more L1)
-   // container scan of the Mutations action: k1_and_popcount (one CTA per work item, kernels_action.cuh) unless SB_K1=stream
-   // selects k1_stream (one persistent CTA per SM, kernels_stream.cuh: bit-exact, but 1.6x slower so far -- DESIGN.md).
-   // Tests run both.
-   bool classic_k1 = !(getenv("SB_K1") != nullptr && std::string(getenv("SB_K1")) == "stream");
+   uint32_t k1_resident = 4;           // CTAs of k1_scan per SM (occupancy query at finalize)
+   // multi-rank: collectives of one communicator must be issued in one order on every rank (sb_comm_enter)
+   std::mutex ticket_mutex;
+   std::condition_variable ticket_cv;
+   uint64_t next_ticket = 0;
+   bool ticket_held = false;
 
    std::vector<std::unique_ptr<HostStore>> stores;
    std::vector<std::unique_ptr<Sequence>> seqs;
@@ -269,14 +277,13 @@ int sb_bitmap_add_portable(sb_db* db, uint32_t partition, const void* bytes, siz
          rc.size = c.kind == KIND_BITSET ? c.card : c.size;
          rc.key = c.key;
          rc.kind = c.kind;
-         const uint32_t n16 = payloadU16(c);
-         db->reg_pool.insert(db->reg_pool.end(), c.data, c.data + n16);
+         appendPayload(db->reg_pool, c);
          db->reg_containers.push_back(rc);
          bm.n_containers++;
          uint32_t last = 0;
-         if (c.kind == KIND_ARRAY) last = c.data[c.size - 1];
-         else if (c.kind == KIND_RUN) last = uint32_t(c.data[2 * (c.size - 1)]) + c.data[2 * (c.size - 1) + 1];
-         else { const uint64_t* w = reinterpret_cast<const uint64_t*>(c.data); for (int k = 1023; k >= 0; --k) { uint64_t x; memcpy(&x, w + k, 8); if (x) { last = uint32_t(k) * 64 + 63 - __builtin_clzll(x); break; } } }
+         if (c.kind == KIND_ARRAY) last = c.u16(c.size - 1);
+         else if (c.kind == KIND_RUN) last = uint32_t(c.u16(2 * (c.size - 1))) + c.u16(2 * (c.size - 1) + 1);
+         else { for (int k = 1023; k >= 0; --k) { const uint64_t x = c.u64(k); if (x) { last = uint32_t(k) * 64 + 63 - __builtin_clzll(x); break; } } }
          bm.max_value = (uint32_t(c.key) << 16) | last;
       });
       *bitmap_id = uint32_t(db->reg_bitmaps.size());
@@ -328,8 +335,7 @@ int sb_store_add(sb_db* db, uint32_t partition, const char* name, int alphabet, 
             SB_REQUIRE(uint64_t(c.key) * 65536 < std::max<uint64_t>(n_rows, 1), "a position bitmap holds row ids beyond sequence_count");
             if (is_deleted) return;
             TmpContainer t{uint32_t(slot), c.key, c.kind, c.kind == KIND_BITSET ? c.card : c.size, st->payload.size()};
-            const uint32_t n16 = payloadU16(c);
-            st->payload.insert(st->payload.end(), c.data, c.data + n16);
+            appendPayload(st->payload, c);
             st->containers.push_back(t);
             st->alg_bytes += (c.kind == KIND_BITSET ? 8192 : c.kind == KIND_ARRAY ? 2 * c.size : 4 * c.size) + 8;
             st->dir_bytes += 8;
@@ -348,14 +354,13 @@ int sb_store_add(sb_db* db, uint32_t partition, const char* name, int alphabet, 
                else st->miss_iv.push_back(make_uint2(start, end));
             };
             if (c.kind == KIND_RUN) {
-               for (uint32_t r = 0; r < c.size; ++r) push(base + c.data[2 * r], base + c.data[2 * r] + c.data[2 * r + 1] + 1);
+               for (uint32_t r = 0; r < c.size; ++r) push(base + c.u16(2 * r), base + c.u16(2 * r) + c.u16(2 * r + 1) + 1);
                bytes += 4 * c.size;
             } else if (c.kind == KIND_ARRAY) {
-               for (uint32_t k = 0; k < c.size; ++k) push(base + c.data[k], base + c.data[k] + 1);
+               for (uint32_t k = 0; k < c.size; ++k) push(base + c.u16(k), base + c.u16(k) + 1);
                bytes += 2 * c.size;
             } else {
-               const uint64_t* w = reinterpret_cast<const uint64_t*>(c.data);
-               for (uint32_t k = 0; k < 1024; ++k) { uint64_t x; memcpy(&x, w + k, 8); while (x) { const uint32_t bit = __builtin_ctzll(x); push(base + k * 64 + bit, base + k * 64 + bit + 1); x &= x - 1; } }
+               for (uint32_t k = 0; k < 1024; ++k) { uint64_t x = c.u64(k); while (x) { const uint32_t bit = __builtin_ctzll(x); push(base + k * 64 + bit, base + k * 64 + bit + 1); x &= x - 1; } }
                bytes += 8192;
             }
          });
@@ -388,8 +393,10 @@ int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, 
 
 }  // extern "C"
 
+#include "pipeline.inc"
 #include "api_filter.inc"
 #include "api_action.inc"
+#include "api_query.inc"
 
 #ifdef SB_K1_TIMELINE
 // diagnostics build (tools/k1_experiment.py): per-CTA time stamps of the container scan

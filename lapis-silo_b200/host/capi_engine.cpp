@@ -26,17 +26,6 @@ struct QueryState {
    std::map<std::string, std::vector<sb_mutation_row>> rows;   // or the rows selected on the device from a reduced device table
 };
 
-// A query compiled and lowered once (plans kept): the device-resident replay used for kernel timing.
-struct PreparedQuery {
-   const DeviceDatabase* device_db;
-   Query query;
-   std::vector<operators::OperatorPtr> trees;
-   std::vector<DeviceDatabase::Plan> plans;
-   std::vector<const sb_node*> plan_ptrs;
-   std::vector<uint32_t> plan_sizes, partitions;
-   std::vector<std::string> names;
-};
-
 }  // namespace
 
 extern "C" {
@@ -199,52 +188,91 @@ char* silo_rows_from_table(const void* db_, const char* query_json, const char* 
    return out;
 }
 
-// ---- prepared queries: compile + lower once, replay filter evaluation + action on the device ----
-void* silo_prepared_create(void* engine_, const char* query_json) {
-   PreparedQuery* out = nullptr;
+// ---- prepared queries: compile + lower + upload + locate once, replay the whole query as one submission ----
+void* silo_prepared_create(void* engine_, const char* query_json, int use_graph) {
+   DeviceDatabase::PreparedQuery* out = nullptr;
+   capi::guarded([&] { out = static_cast<DeviceDatabase*>(engine_)->prepare(query_json, use_graph != 0).release(); });
+   return out;
+}
+void silo_prepared_free(void* prepared) { delete static_cast<DeviceDatabase::PreparedQuery*>(prepared); }
+
+// One device-resident step: the rows stay in the library's pinned buffer, nothing is formatted. Returns the number of
+// result rows over all sequences (Aggregated: the count) through `result_rows`.
+int silo_prepared_run_device(void* engine_, void* prepared_, uint64_t* result_rows) {
+   return capi::guarded([&] {
+      auto& p = *static_cast<DeviceDatabase::PreparedQuery*>(prepared_);
+      thread_local DeviceDatabase::FusedResult fused;
+      std::lock_guard<std::mutex> lock(p.mutex);
+      static_cast<DeviceDatabase*>(engine_)->runPrepared(p, fused);
+      if (result_rows) {
+         uint64_t n = 0;
+         if (p.query.action.type == ActionType::AGGREGATED) n = fused.count();
+         else for (const auto& s : fused.sequences) n += s.rows.size();
+         *result_rows = n;
+      }
+   });
+}
+// The response text of a prepared query (what silo_engine_execute returns for the same text)
+char* silo_prepared_run(void* engine_, void* prepared_) {
+   char* out = nullptr;
    capi::guarded([&] {
       auto& engine = *static_cast<DeviceDatabase*>(engine_);
-      auto p = std::make_unique<PreparedQuery>();
-      p->device_db = &engine;
-      p->query = parseQuery(query_json);
-      if (p->query.action.type != ActionType::AGGREGATED) p->names = engine.mutationSequenceNames(p->query.action);
-      p->plans.resize(engine.owned.size());
-      for (uint32_t local = 0; local < engine.owned.size(); ++local) {
-         p->trees.push_back(p->query.filter->compile(engine.db, *engine.db.partitions[engine.owned[local]], filter::AmbiguityMode::NONE));
-         engine.lower(*p->trees.back(), local, p->plans[local]);
-         p->plan_ptrs.push_back(p->plans[local].nodes.data());
-         p->plan_sizes.push_back(static_cast<uint32_t>(p->plans[local].nodes.size()));
-         p->partitions.push_back(local);
-      }
-      out = p.release();
+      auto& p = *static_cast<DeviceDatabase::PreparedQuery*>(prepared_);
+      DeviceDatabase::FusedResult fused;
+      { std::lock_guard<std::mutex> lock(p.mutex); engine.runPrepared(p, fused); }
+      out = capi::dupString(engine.responseText(p.query.action, p.names, fused));
    });
    return out;
 }
-void silo_prepared_free(void* prepared) { delete static_cast<PreparedQuery*>(prepared); }
-
-// One device-resident step: filters of all local partitions, then the count table of sequence `name_index`
-// into `device_counts` (device memory). With device_counts == NULL only the filters run (Aggregated).
-// Also reports the algorithmic bytes of the step when `alg_bytes` is given (costs a filter export: not for timed steps).
-int silo_prepared_run_device(void* prepared_, uint32_t name_index, void* device_counts, uint64_t len, uint32_t* aggregated_count,
-                             uint64_t* alg_bytes, uint64_t* k1_bytes) {
+// The uint32 count table of sequence `name_index` of the last run, copied to the host (checksums, parity tests)
+int silo_prepared_table(void* prepared_, uint32_t name_index, uint32_t* out, uint64_t len) {
    return capi::guarded([&] {
-      auto& p = *static_cast<PreparedQuery*>(prepared_);
-      DeviceDatabase::EvaluatedFilters filters;
-      filters.handle = p.device_db->handle;
-      filters.partitions = p.partitions;
-      filters.results.assign(p.partitions.size(), nullptr);
-      engine::check(sb_filter_eval_batch(filters.handle, static_cast<uint32_t>(p.partitions.size()), p.partitions.data(), p.plan_ptrs.data(), p.plan_sizes.data(), filters.results.data()));
-      if (aggregated_count) *aggregated_count = p.device_db->aggregatedCount(filters);
-      if (device_counts) {
-         int produced = 0;
-         engine::check(sb_mutations_device(filters.handle, p.names.at(name_index).c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(),
-                                           filters.results.data(), device_counts, len, &produced));
-      }
-      if (alg_bytes) {
-         engine::check(sb_mutations_algorithmic_bytes(filters.handle, p.names.at(name_index).c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(),
-                                                      filters.results.data(), alg_bytes, k1_bytes));
-      }
+      auto& p = *static_cast<DeviceDatabase::PreparedQuery*>(prepared_);
+      if (!p.handle) throw std::runtime_error("prepared query owns no partition");
+      const void* device = nullptr;
+      size_t n = 0;
+      engine::check(sb_query_table_device(p.handle, name_index, &device, &n));
+      if (n != len) throw std::runtime_error("count table size mismatch");
+      engine::check(sb_copy_from_device(out, device, n * sizeof(uint32_t)));
    });
+}
+// Algorithmic bytes of the prepared Mutations query for sequence `name_index`: evaluates the filters through the
+// split entry points (costs a filter export: not for timed steps).
+int silo_prepared_bytes(void* engine_, void* prepared_, uint32_t name_index, uint64_t* alg_bytes, uint64_t* k1_bytes) {
+   return capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      auto& p = *static_cast<DeviceDatabase::PreparedQuery*>(prepared_);
+      DeviceDatabase::EvaluatedFilters filters;
+      filters.handle = engine.handle;
+      filters.partitions = p.compiled.partitions;
+      filters.results.assign(filters.partitions.size(), nullptr);
+      if (filters.partitions.empty()) { *alg_bytes = 0; *k1_bytes = 0; return; }
+      engine::check(sb_filter_eval_batch(engine.handle, static_cast<uint32_t>(filters.partitions.size()), filters.partitions.data(), p.compiled.plan_ptrs.data(), p.compiled.plan_sizes.data(), filters.results.data()));
+      engine::check(sb_mutations_algorithmic_bytes(engine.handle, p.names.at(name_index).c_str(), static_cast<uint32_t>(filters.results.size()), filters.partitions.data(),
+                                                   filters.results.data(), alg_bytes, k1_bytes));
+   });
+}
+void silo_engine_set_plan_cache(void* engine_, int enabled) { static_cast<DeviceDatabase*>(engine_)->setPlanCache(enabled != 0); }
+
+// Multi-GPU (one process per GPU, sb_comm_init done): every rank calls with the same query text in the same order; the
+// library sums the count tables over the ranks inside the query's one submission. Rank 0 gets the response text, the
+// other ranks an empty string. Mutations / AminoAcidMutations only (an Aggregated count is one integer the caller sums).
+char* silo_engine_execute_sharded(void* engine_, const char* query_json, int is_root) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      Query query = parseQuery(query_json);
+      const Action& action = query.action;
+      if (action.type == ActionType::AGGREGATED) throw QueryCompilationException("silo_engine_execute_sharded serves Mutations actions");
+      action.validateOrderByFields();
+      const std::vector<std::string> names = engine.mutationSequenceNames(action);
+      DeviceDatabase::CompiledFilter cf;
+      engine.compileFilter(*query.filter, cf);
+      DeviceDatabase::FusedResult fused;
+      engine.runFused(cf, names, action.alphabetId(), action.min_proportion, fused);
+      out = capi::dupString(is_root ? engine.responseText(action, names, fused) : std::string());
+   });
+   return out;
 }
 
 // Test hook for the host worker pool (tests/test_host_cpu.py; no device involved): runs n_jobs jobs that add

@@ -171,7 +171,7 @@ class DeviceDatabase {
       } catch (...) { sb_db_free(handle); handle = nullptr; throw; }
    }
    DeviceDatabase(const DeviceDatabase&) = delete;
-   ~DeviceDatabase() { pool_.reset(); if (handle) sb_db_free(handle); }
+   ~DeviceDatabase() { pool_.reset(); cache_.clear(); if (handle) sb_db_free(handle); }
 
    // ---- plan lowering -------------------------------------------------------------------------------
    struct Plan {
@@ -364,61 +364,145 @@ class DeviceDatabase {
       return count;
    }
 
-   QueryResult executeQuery(const std::string& query_string, std::map<std::string, std::vector<uint32_t>>* tables = nullptr) const {
-      HostTrace trace;
-      Query query = parseQuery(query_string);
-      trace.lap("parse");
-      EvaluatedFilters filters = evaluateFilter(*query.filter);
-      trace.lap("filter");
-      return query.action.executeAndOrder([&]() -> QueryResult {
-         if (query.action.type == ActionType::AGGREGATED) {
-            if (!query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+   // ---- one query = one submission (include/silo_b200.h: sb_query_mutations / sb_query_prepare) -----------------------
+   // compile + lower per partition (query_engine.cpp:41-46 does it one partition after the other; the partitions are
+   // independent, so with more than a few of them the worker pool shares the work)
+   struct CompiledFilter {
+      std::vector<operators::OperatorPtr> trees;
+      std::vector<Plan> plans;
+      std::vector<const sb_node*> plan_ptrs;
+      std::vector<uint32_t> plan_sizes, partitions;
+   };
+   void compileFilter(const filter::Expression& expression, CompiledFilter& out) const {
+      const size_t n = owned.size();
+      out.trees.resize(n);
+      out.plans.assign(n, Plan());
+      auto one = [&](size_t local) {
+         out.trees[local] = expression.compile(db, *db.partitions[owned[local]], filter::AmbiguityMode::NONE);
+         lower(*out.trees[local], static_cast<uint32_t>(local), out.plans[local]);
+      };
+      if (n >= 8) workers().run(n, one);
+      else for (size_t local = 0; local < n; ++local) one(local);
+      out.plan_ptrs.clear(); out.plan_sizes.clear(); out.partitions.clear();
+      for (uint32_t local = 0; local < n; ++local) {
+         out.plan_ptrs.push_back(out.plans[local].nodes.data());
+         out.plan_sizes.push_back(static_cast<uint32_t>(out.plans[local].nodes.size()));
+         out.partitions.push_back(local);
+      }
+   }
+
+   struct FusedResult {
+      std::vector<SequenceRows> sequences;      // per requested sequence
+      std::vector<uint64_t> cardinalities;      // per local partition
+      uint32_t count() const { uint32_t c = 0; for (uint64_t v : cardinalities) c += static_cast<uint32_t>(v); return c; }   // aggregated.cpp:58-66 (uint32 accumulation)
+   };
+   // runs `call(out array, cardinalities)` until every sequence's rows fit
+   template <typename Call>
+   void runWithRowBuffers(size_t n_sequences, size_t n_partitions, FusedResult& result, Call&& call) const {
+      result.sequences.resize(n_sequences);
+      result.cardinalities.assign(n_partitions, 0);
+      std::vector<sb_sequence_rows> out(n_sequences);
+      for (auto& seq : result.sequences) seq.rows.resize(std::max<size_t>(seq.rows.size(), 1024));
+      for (;;) {
+         for (size_t k = 0; k < n_sequences; ++k) out[k] = sb_sequence_rows{result.sequences[k].rows.data(), result.sequences[k].rows.size(), 0, 0, 0};
+         check(call(out.data(), result.cardinalities.data()));
+         bool again = false;
+         for (size_t k = 0; k < n_sequences; ++k) if (out[k].n_rows > result.sequences[k].rows.size()) { result.sequences[k].rows.resize(out[k].n_rows); again = true; }
+         if (!again) break;
+      }
+      for (size_t k = 0; k < n_sequences; ++k) { result.sequences[k].rows.resize(out[k].n_rows); result.sequences[k].produced = out[k].produced != 0; }
+   }
+   static std::vector<const char*> cNames(const std::vector<std::string>& names) {
+      std::vector<const char*> out;
+      for (const auto& n : names) out.push_back(n.c_str());
+      return out;
+   }
+   void runFused(const CompiledFilter& cf, const std::vector<std::string>& names, int alphabet_id, double min_proportion, FusedResult& result) const {
+      const auto& valid = alphabetById(alphabet_id).valid_mutation_symbols;
+      const std::vector<const char*> c_names = cNames(names);
+      if (cf.partitions.empty()) { result.sequences.assign(names.size(), SequenceRows()); result.cardinalities.clear(); return; }
+      runWithRowBuffers(names.size(), cf.partitions.size(), result, [&](sb_sequence_rows* out, uint64_t* cards) {
+         return sb_query_mutations(handle, static_cast<uint32_t>(cf.partitions.size()), cf.partitions.data(), cf.plan_ptrs.data(), cf.plan_sizes.data(),
+                                   static_cast<uint32_t>(names.size()), c_names.data(), min_proportion, valid.data(), static_cast<uint32_t>(valid.size()), out, cards);
+      });
+   }
+
+   // A query kept on the device for replay (sb_query): what the plan cache holds and what silo_prepared_* hands out.
+   struct PreparedQuery {
+      Query query;
+      std::vector<std::string> names;
+      CompiledFilter compiled;
+      sb_query* handle = nullptr;
+      std::mutex mutex;
+      PreparedQuery() = default;
+      PreparedQuery(const PreparedQuery&) = delete;
+      ~PreparedQuery() { if (handle) sb_query_free(handle); }
+   };
+   std::unique_ptr<PreparedQuery> prepare(const std::string& query_string, bool use_graph) const {
+      auto p = std::make_unique<PreparedQuery>();
+      p->query = parseQuery(query_string);
+      p->query.action.validateOrderByFields();
+      if (p->query.action.type == ActionType::AGGREGATED) {
+         if (!p->query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields cannot be prepared");
+      } else {
+         p->names = mutationSequenceNames(p->query.action);
+      }
+      compileFilter(*p->query.filter, p->compiled);
+      if (owned.empty()) return p;
+      const int alphabet_id = p->query.action.type == ActionType::AGGREGATED ? 0 : p->query.action.alphabetId();
+      const auto& valid = alphabetById(alphabet_id).valid_mutation_symbols;
+      const std::vector<const char*> c_names = cNames(p->names);
+      check(sb_query_prepare(handle, static_cast<uint32_t>(p->compiled.partitions.size()), p->compiled.partitions.data(), p->compiled.plan_ptrs.data(), p->compiled.plan_sizes.data(),
+                             static_cast<uint32_t>(p->names.size()), c_names.data(), p->query.action.min_proportion, valid.data(), static_cast<uint32_t>(valid.size()),
+                             use_graph ? 1 : 0, &p->handle));
+      return p;
+   }
+   void runPrepared(PreparedQuery& p, FusedResult& result) const {
+      if (!p.handle) { result.sequences.assign(p.names.size(), SequenceRows()); result.cardinalities.clear(); return; }
+      runWithRowBuffers(p.names.size(), p.compiled.partitions.size(), result, [&](sb_sequence_rows* out, uint64_t* cards) { return sb_query_run(p.handle, out, cards); });
+   }
+
+   QueryResult resultFromRows(const Action& action, const std::vector<std::string>& names, const FusedResult& fused) const {
+      return action.executeAndOrder([&]() -> QueryResult {
+         if (action.type == ActionType::AGGREGATED) {
             QueryResultEntry entry;
-            entry.fields["count"] = static_cast<int32_t>(aggregatedCount(filters));   // aggregated.cpp:58-66
+            entry.fields["count"] = static_cast<int32_t>(fused.count());   // aggregated.cpp:58-66
             return QueryResult{{entry}};
          }
-         const int alphabet_id = query.action.alphabetId();
+         const int alphabet_id = action.alphabetId();
          QueryResult result;
-         std::vector<uint32_t> counts;
-         const std::vector<std::string> names = mutationSequenceNames(query.action);   // mutations.cpp:258-270
-         const std::vector<SequenceRows> all_rows = mutationRowsAll(filters, names, alphabet_id, query.action.min_proportion);
-         trace.lap("counts+select");
-         for (size_t k = 0; k < names.size(); ++k) {
-            if (!all_rows[k].produced) continue;
-            const std::string& name = names[k];
-            const std::vector<sb_mutation_row>& rows = all_rows[k].rows;
-            addRowsToOutput(name, alphabetById(alphabet_id), db.getReferences(alphabet_id).at(name), rows, result.query_result);
-            trace.lap("rows");
-            if (tables && mutationCounts(filters, name, alphabet_id, counts)) (*tables)[name] = counts;   // the whole table, for the parity tests
+         for (size_t k = 0; k < names.size(); ++k) {      // mutations.cpp:258-270
+            if (!fused.sequences[k].produced) continue;
+            addRowsToOutput(names[k], alphabetById(alphabet_id), db.getReferences(alphabet_id).at(names[k]), fused.sequences[k].rows, result.query_result);
          }
          return result;
       });
    }
 
-   // The response body {"queryResult": [...]} of a query. Mutations without orderByFields / limit / offset -- the common
-   // case -- is written straight from the selected rows (the same text as dumpJson(executeQuery(...)): keys in the
-   // order of the entry map, doubles through json::Value::writeDouble); everything else takes the general path.
-   std::string executeQueryJson(const std::string& query_string) const {
-      HostTrace trace;
+   QueryResult executeQuery(const std::string& query_string) const {
       Query query = parseQuery(query_string);
-      const Action& action = query.action;
-      if (action.type == ActionType::AGGREGATED || !action.order_by_fields.empty() || action.limit || action.offset) return dumpJson(executeQuery(query_string));
-      trace.lap("parse");
-      action.validateOrderByFields();
-      EvaluatedFilters filters = evaluateFilter(*query.filter);
-      trace.lap("filter");
+      if (query.action.type == ActionType::AGGREGATED && !query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+      std::vector<std::string> names;
+      if (query.action.type != ActionType::AGGREGATED) names = mutationSequenceNames(query.action);
+      CompiledFilter cf;
+      compileFilter(*query.filter, cf);
+      FusedResult fused;
+      runFused(cf, names, query.action.type == ActionType::AGGREGATED ? 0 : query.action.alphabetId(), query.action.min_proportion, fused);
+      return resultFromRows(query.action, names, fused);
+   }
+
+   // Mutations rows -> the response text, straight from the selected rows (the same text as dumpJson(resultFromRows(...)):
+   // keys in the order of the entry map, doubles through json::Value::writeDouble)
+   std::string rowsToJson(const Action& action, const std::vector<std::string>& names, const FusedResult& fused) const {
       const int alphabet_id = action.alphabetId();
       const Alphabet& alphabet = alphabetById(alphabet_id);
       std::string out = "{\"queryResult\":[";
       bool first = true;
       char number[16];
-      const std::vector<std::string> names = mutationSequenceNames(action);
-      const std::vector<SequenceRows> all_rows = mutationRowsAll(filters, names, alphabet_id, action.min_proportion);
-      trace.lap("counts+select");
       for (size_t k = 0; k < names.size(); ++k) {
-         if (!all_rows[k].produced) continue;
+         if (!fused.sequences[k].produced) continue;
          const std::string& name = names[k];
-         const std::vector<sb_mutation_row>& rows = all_rows[k].rows;
+         const std::vector<sb_mutation_row>& rows = fused.sequences[k].rows;
          const auto& reference = db.getReferences(alphabet_id).at(name);
          std::string quoted_name;
          json::Value::writeString(quoted_name, name);
@@ -438,13 +522,81 @@ class DeviceDatabase {
             out += quoted_name;
             out += '}';
          }
-         trace.lap("rows");
       }
       out += "]}";
       return out;
    }
+   std::string responseText(const Action& action, const std::vector<std::string>& names, const FusedResult& fused) const {
+      if (action.type == ActionType::AGGREGATED || !action.order_by_fields.empty() || action.limit || action.offset) return dumpJson(resultFromRows(action, names, fused));
+      return rowsToJson(action, names, fused);
+   }
+
+   // The response body {"queryResult": [...]} of a query. A query text seen before is answered from the plan cache: the
+   // compiled + lowered plans stay on the device as a prepared query (from the second sighting on, as a CUDA graph).
+   std::string executeQueryJson(const std::string& query_string) const {
+      HostTrace trace;
+      if (plan_cache_enabled_) {
+         std::shared_ptr<PreparedQuery> hit = cacheLookup(query_string);
+         if (hit) {
+            trace.lap("cache");
+            FusedResult fused;
+            { std::lock_guard<std::mutex> lock(hit->mutex); runPrepared(*hit, fused); }
+            trace.lap("run");
+            return responseText(hit->query.action, hit->names, fused);
+         }
+      }
+      Query query = parseQuery(query_string);
+      const Action& action = query.action;
+      trace.lap("parse");
+      if (action.type == ActionType::AGGREGATED && !action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+      action.validateOrderByFields();
+      std::vector<std::string> names;
+      if (action.type != ActionType::AGGREGATED) names = mutationSequenceNames(action);
+      CompiledFilter cf;
+      compileFilter(*query.filter, cf);
+      trace.lap("compile+lower");
+      FusedResult fused;
+      runFused(cf, names, action.type == ActionType::AGGREGATED ? 0 : action.alphabetId(), action.min_proportion, fused);
+      trace.lap("run");
+      return responseText(action, names, fused);
+   }
+   void setPlanCache(bool enabled) { std::lock_guard<std::mutex> lock(cache_mutex_); plan_cache_enabled_ = enabled; cache_.clear(); cache_order_.clear(); }
 
   private:
+   // Plan cache: query text -> prepared query. The first sighting of a text only counts it; the second prepares it (compile,
+   // lower, upload, locate, graph capture), later ones replay. A busy entry (another thread is running it) is a miss.
+   struct CacheEntry { uint32_t sightings = 0; std::shared_ptr<PreparedQuery> prepared; };
+   static constexpr size_t PLAN_CACHE_ENTRIES = 64;
+   mutable std::mutex cache_mutex_;
+   mutable std::unordered_map<std::string, CacheEntry> cache_;
+   mutable std::deque<std::string> cache_order_;
+   mutable bool plan_cache_enabled_ = getenv("SILO_PLAN_CACHE") == nullptr || std::string(getenv("SILO_PLAN_CACHE")) != "0";
+   std::shared_ptr<PreparedQuery> cacheLookup(const std::string& text) const {
+      bool build = false;
+      {
+         std::lock_guard<std::mutex> lock(cache_mutex_);
+         auto it = cache_.find(text);
+         if (it == cache_.end()) {
+            if (cache_.size() >= PLAN_CACHE_ENTRIES) { cache_.erase(cache_order_.front()); cache_order_.pop_front(); }
+            cache_[text].sightings = 1;
+            cache_order_.push_back(text);
+            return nullptr;
+         }
+         if (it->second.prepared) {
+            std::unique_lock<std::mutex> busy(it->second.prepared->mutex, std::try_to_lock);
+            return busy.owns_lock() ? it->second.prepared : nullptr;
+         }
+         build = ++it->second.sightings == 2;
+      }
+      if (!build) return nullptr;
+      std::shared_ptr<PreparedQuery> made;
+      try { made = prepare(text, /*use_graph=*/true); } catch (...) { return nullptr; }   // e.g. a query the one-shot path rejects with its own message
+      std::lock_guard<std::mutex> lock(cache_mutex_);
+      auto it = cache_.find(text);
+      if (it != cache_.end()) it->second.prepared = made;
+      return made;
+   }
+
    WorkerPool& workers() const {
       std::lock_guard<std::mutex> lock(pool_mutex_);
       if (!pool_) pool_ = std::make_unique<WorkerPool>(6);

@@ -64,9 +64,14 @@ def host():
         "silo_query_set_table_device": (ctypes.c_int, [vp, u32, vp]),
         "silo_query_finish": (vp, [vp, u32]),
         "silo_rows_from_table": (vp, [vp, cp, cp, vp, u64]),
-        "silo_prepared_create": (vp, [vp, cp]),
+        "silo_prepared_create": (vp, [vp, cp, ctypes.c_int]),
         "silo_prepared_free": (None, [vp]),
-        "silo_prepared_run_device": (ctypes.c_int, [vp, u32, vp, u64, pu32, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
+        "silo_prepared_run_device": (ctypes.c_int, [vp, vp, ctypes.POINTER(u64)]),
+        "silo_prepared_run": (vp, [vp, vp]),
+        "silo_prepared_table": (ctypes.c_int, [vp, u32, vp, u64]),
+        "silo_prepared_bytes": (ctypes.c_int, [vp, vp, u32, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
+        "silo_engine_set_plan_cache": (None, [vp, ctypes.c_int]),
+        "silo_engine_execute_sharded": (vp, [vp, cp, ctypes.c_int]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32]),
         "silo_synth_owned_count": (u32, [vp]),
         "silo_synth_owned": (u32, [vp, u32]),
@@ -288,6 +293,14 @@ class Engine:
         """The response body as the reference's HTTP handler writes it ({"queryResult": [...]}), not parsed."""
         return _take_string(host().silo_engine_execute(self.handle, query_json.encode() if isinstance(query_json, str) else query_json))
 
+    def set_plan_cache(self, enabled):
+        """the engine's query-text -> prepared-query cache (on by default); switching clears it"""
+        host().silo_engine_set_plan_cache(self.handle, int(enabled))
+
+    def execute_sharded(self, query_json, is_root):
+        """multi-GPU: every rank calls with the same text in the same order; rank 0 gets the response text"""
+        return _take_string(host().silo_engine_execute_sharded(self.handle, query_json.encode() if isinstance(query_json, str) else query_json, int(is_root)))
+
     def mutation_counts(self, query, sequence_name, table_len):
         q = query if isinstance(query, str) else json.dumps(query)
         out = np.zeros(table_len, dtype=np.uint32)
@@ -406,22 +419,41 @@ def pool_stats(engine):
 
 
 class Prepared:
-    """A query compiled and lowered once; run_device() replays filter evaluation + the action on the GPU."""
+    """A query compiled, lowered, uploaded and located once (sb_query_prepare); run*() replays filter evaluation + action as
+    one submission -- with use_graph as one CUDA graph launch."""
 
-    def __init__(self, engine, query):
+    def __init__(self, engine, query, use_graph=True):
         q = query if isinstance(query, str) else json.dumps(query)
         self.engine = engine
-        self.handle = host().silo_prepared_create(engine.handle, q.encode())
+        self.handle = host().silo_prepared_create(engine.handle, q.encode(), int(use_graph))
         if not self.handle:
             raise _error()
 
-    def run_device(self, name_index=0, device_ptr=None, table_len=0, want_bytes=False, want_count=False):
-        count, total, k1 = ctypes.c_uint32(), ctypes.c_uint64(), ctypes.c_uint64()
-        rc = host().silo_prepared_run_device(self.handle, name_index, device_ptr, table_len, ctypes.byref(count) if want_count else None,
-                                            ctypes.byref(total) if want_bytes else None, ctypes.byref(k1) if want_bytes else None)
-        if rc != 0:
+    def run_device(self):
+        """one device-resident step; returns the number of result rows (Aggregated: the count)"""
+        n = ctypes.c_uint64()
+        if host().silo_prepared_run_device(self.engine.handle, self.handle, ctypes.byref(n)) != 0:
             raise _error()
-        return {"count": count.value, "alg_bytes": total.value, "k1_bytes": k1.value}
+        return n.value
+
+    def run_text(self):
+        return _take_string(host().silo_prepared_run(self.engine.handle, self.handle))
+
+    def run(self):
+        return json.loads(self.run_text())["queryResult"]
+
+    def table(self, name_index, table_len):
+        """uint32 count table of sequence `name_index` of the last run"""
+        out = np.zeros(table_len, dtype=np.uint32)
+        if host().silo_prepared_table(self.handle, name_index, out.ctypes.data, table_len) != 0:
+            raise _error()
+        return out
+
+    def algorithmic_bytes(self, name_index=0):
+        total, k1 = ctypes.c_uint64(), ctypes.c_uint64()
+        if host().silo_prepared_bytes(self.engine.handle, self.handle, name_index, ctypes.byref(total), ctypes.byref(k1)) != 0:
+            raise _error()
+        return {"alg_bytes": total.value, "k1_bytes": k1.value}
 
     def close(self):
         if self.handle:

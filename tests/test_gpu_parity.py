@@ -233,12 +233,11 @@ def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
     assert failures == []
 
 
-@pytest.mark.parametrize("env", [{"SB_K1": "item"}, {"SB_K1": "stream"}, {"SB_K1": "stream", "SB_K1_CTAS": "1"}, {"SB_K1": "stream", "SB_K1_CTAS": "3"},
-                                 {"SB_K1": "stream", "SB_K1_CTAS": "7"}, {"SB_K1": "stream", "SB_K1_CTAS": "4000"}],
+@pytest.mark.parametrize("env", [{"SB_K1_CTAS": "1"}, {"SB_K1_CTAS": "3"}, {"SB_K1_CTAS": "7"}, {"SB_K1_CTAS": "4000"}, {"SB_ITEM_CAP_KB": "4"}],
                          ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
 def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch):
-    """both container-scan kernels (k1_and_popcount: one CTA per work item; k1_stream: persistent CTAs) and odd numbers of
-    persistent CTAs (runs that cross slabs and partitions, one CTA with everything, more CTAs than items) against the oracle"""
+    """the container scan with odd numbers of persistent CTAs (one CTA takes every item, more CTAs than items) and with tiny
+    work items (many items per segment), against the oracle"""
     pysilo, oracle = libs
     for k, v in env.items():
         monkeypatch.setenv(k, v)      # read when the device database is created
@@ -253,22 +252,57 @@ def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch)
             engine.close()
 
 
+def test_prepared_queries_and_plan_cache(libs, synth_medium, medium_engine, synth_small, small_engine):
+    """a prepared query (with and without a CUDA graph) and the engine's plan cache replay the same tables and texts as the
+    one-shot path, run after run; Aggregated and AminoAcidMutations over all genes included"""
+    pysilo, oracle = libs
+    for db, engine, length in ((synth_medium, medium_engine, 29903), (synth_small, small_engine, 3000)):
+        for f in synthetic_filters(db):
+            q = {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f}
+            want_table, produced = oracle.mutation_counts(db, q, "main", 16 * length, faithful=False)
+            want_rows = oracle.execute(db, q, faithful=False)
+            for use_graph in (False, True):
+                prepared = pysilo.Prepared(engine, q, use_graph=use_graph)
+                try:
+                    for _ in range(3):
+                        assert prepared.run() == want_rows
+                        if produced:
+                            assert np.array_equal(prepared.table(0, 16 * length), want_table)
+                finally:
+                    prepared.close()
+            engine.set_plan_cache(True)
+            for _ in range(4):      # miss, prepare, hit, hit
+                assert engine.execute(q) == want_rows
+            agg = {"action": {"type": "Aggregated"}, "filterExpression": f}
+            prepared = pysilo.Prepared(engine, agg)
+            assert prepared.run() == oracle.execute(db, agg) and prepared.run_device() == oracle.execute(db, agg)[0]["count"]
+            prepared.close()
+    aa = {"action": {"type": "AminoAcidMutations", "minProportion": 0.01}, "filterExpression": synthetic_filters(synth_small)[2]}
+    prepared = pysilo.Prepared(small_engine, aa)
+    for _ in range(2):
+        assert prepared.run() == oracle.execute(synth_small, aa)
+    prepared.close()
+
+
 def test_in_library_reduce_single_rank(libs, synth_small):
-    """sb_comm_init with a world of one rank: the NCCL reduce that ends sb_mutations_device must leave the table as it is
-    (the multi-rank sum is exercised by bench.py --gpus N and, on the CPU, by tests/test_distributed_cpu.py)"""
+    """sb_comm_init with a world of one rank: the NCCL reduce inside the query's submission must leave the tables as they are
+    (the multi-rank sum: tests/test_gpu_multirank.py on two GPUs and, on the CPU, tests/test_distributed_cpu.py)"""
     import torch      # before the library loads NCCL: the process keeps one libnccl.so.2, and torch needs its own
     pysilo, oracle = libs
     engine = pysilo.Engine(synth_small, 0)
     try:
         pysilo.comm_init(engine, pysilo.comm_unique_id(), 0, 1)
-        f = synthetic_filters(synth_small)[3]
-        q = {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f}
-        counts = torch.zeros(16 * 3000, dtype=torch.int32, device="cuda:0")
-        prepared = pysilo.Prepared(engine, q)
-        prepared.run_device(0, counts.data_ptr(), 16 * 3000)
-        want, _ = oracle.mutation_counts(synth_small, q, "main", 16 * 3000)
-        assert np.array_equal(counts.cpu().numpy().view(np.uint32), want)
-        prepared.close()
+        for f in synthetic_filters(synth_small)[1:4]:
+            q = {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f}
+            assert json.loads(engine.execute_sharded(json.dumps(q), True))["queryResult"] == oracle.execute(synth_small, q)
+            counts = torch.zeros(16 * 3000, dtype=torch.int32, device="cuda:0")
+            dq = pysilo.DistributedQuery(engine, q)
+            produced = dq.local_table_device(0, counts.data_ptr(), 16 * 3000)
+            want, want_any = oracle.mutation_counts(synth_small, q, "main", 16 * 3000)
+            assert produced == want_any
+            if produced:
+                assert np.array_equal(counts.cpu().numpy().view(np.uint32), want)
+            dq.close()
         pysilo.comm_free(engine)
     finally:
         engine.close()
