@@ -1,21 +1,22 @@
 #!/usr/bin/env python
-"""bench.py — Mutations-action queries/s on synthetic SARS-CoV-2-shaped data (BASELINE.json).
+"""bench.py — Mutations-action queries/s on synthetic SARS-CoV-2-shaped data (BASELINE.json, configuration C5).
 
-One "step" = one nucleotide Mutations query (minProportion 0.05) under the N-Of filter of BASELINE config
-C3 (3 of 10 clade-defining NucleotideEquals) over one shard of 10 M sequences x 29,903 nt. The path shards by
-DatabasePartition: with N GPUs every rank holds the DatabasePartitions of its own 10 M-sequence shard (weak
-scaling: an N x 10 M-sequence database; the shards are statistically identical, generated from the same seed), a
-step runs the query on every shard and sums the per-rank count tables with an NCCL reduce, and `value` counts one
-query per shard: N x steps / time (at N = 1 plainly queries/s). `--strong` instead shards ONE database of
-`--rows` sequences over the ranks (the 40 M-sequence configuration C5: `--rows 40000000 --strong`).
+Workload: ONE database of --rows (default 40 M) synthetic sequences x 29,903 nt in lineage DatabasePartitions
+(seed 0x51100005), sharded over the N ranks by DatabasePartition (strong scaling: N = 1 holds all of it, 4 GB of index).
+One "step" = one nucleotide Mutations query (minProportion 0.05) out of a rotation of 8 distinct N-Of(3 of 10) filters over
+clade-defining NucleotideEquals (different picks -> different sets of partial partitions, different |F|); step i runs
+query i mod 8. For N > 1 every rank answers the query on its partitions and the count tables are summed inside the query's
+submission (ncclReduce over NVLink, valid-symbol rows only); rank 0 selects the rows.
 
-    value  queries/s with the index resident in HBM and the query compiled once: filter kernels + count
-           kernels (+ NCCL reduce), timed with CUDA events on the library's stream, max over ranks
-    e2e    queries/s through the public call a user makes: query JSON in -> result JSON out, i.e.
-           parse, FilterExpression -> Operator compile, plan upload (H2D), kernels, count table download
-           (D2H), thresholds / proportions on the host
-    --impl reference   the CPU restatement of the reference's algorithm (oracle/, all host threads) on a
-           bounded sample of the same workload (the reference itself cannot be built here)
+    value  queries/s with the queries prepared (plans resident in HBM, one CUDA graph launch per query at N = 1), CUDA
+           events around the timed steps, max over ranks
+    e2e    queries/s through the call a user makes: query JSON in -> response JSON out, plan cache OFF, i.e. every step
+           parses, compiles FilterExpression -> Operator per partition, lowers, uploads the plans (H2D), runs, reads the
+           rows back (D2H) and formats; e2e.cached is the same with the engine's plan cache on
+    --impl reference   the CPU restatement of the reference's algorithm (oracle/, all host threads): the reference itself
+           cannot be built here. Each step runs query 0 on a fixed sample of partitions whose share of the
+           whole query's CPU time was measured by one full pass during set-up; ms_per_step is the time that was measured.
+    --weak replicas of one --rows shard per rank (round-1 mode), --lineage adds the C5 lineage / True queries to the line.
 """
 import argparse
 import json
@@ -25,6 +26,7 @@ import subprocess
 import sys
 import threading
 import time
+import zlib
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
@@ -32,30 +34,46 @@ sys.path.insert(0, str(ROOT / "lapis-silo_b200"))
 
 GENOME_LENGTH = 29903
 SIGMA = 16
+VALID_ROWS = 5            # symbols -, A, C, G, T: the rows of the table anyone reads (and the rows that are reduced)
 METRIC = "mutations_queries_per_s"
 UNIT = "queries/s"
+N_ROTATION = 8
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--rows", type=int, default=int(os.environ.get("SILO_BENCH_ROWS", 10_000_000)))
-    ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x51100003)
+    ap.add_argument("--rows", type=int, default=int(os.environ.get("SILO_BENCH_ROWS", 40_000_000)))
+    ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x51100005)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--strong", action="store_true", help="N > 1: shard one database of --rows sequences over the ranks instead of one shard of --rows per rank")
+    ap.add_argument("--weak", action="store_true", help="N > 1: every rank holds its own shard of --rows sequences (replicated shards) instead of a share of one database")
+    ap.add_argument("--lineage", action="store_true", help="also measure the C5 lineage and True queries (full / partial / empty partitions)")
     ap.add_argument("--in-flight", type=int, default=8, help="queries in flight of the extra throughput measurement (N = 1 only; 0 = skip)")
     return ap.parse_args()
 
 
-def c3_query(db):
-    clade = db.clade_mutations()
-    picks = [clade[(7 * k) % len(clade)] for k in range(10)]
+def nof_query(clade, k):
+    """rotation member k: 3 of 10 clade-defining mutations, picks (7 j + 3 k) mod |clade|; k = 0 is the C3 query of round 1"""
+    picks = [clade[(7 * j + 3 * k) % len(clade)] for j in range(10)]
     return {"action": {"type": "Mutations", "minProportion": 0.05},
             "filterExpression": {"type": "N-Of", "numberOfMatchers": 3, "matchExactly": False,
                                  "children": [{"type": "NucleotideEquals", "position": p + 1, "symbol": s} for p, s in picks]}}
+
+
+def c3_query(db):
+    return nof_query(db.clade_mutations(), 0)
+
+
+def rotation(db):
+    clade = db.clade_mutations()
+    return [nof_query(clade, k) for k in range(N_ROTATION)]
+
+
+def workload_name(rows):
+    return f"C5: {rows} synthetic sequences x {GENOME_LENGTH} nt in lineage partitions, nucleotide Mutations under a rotation of {N_ROTATION} N-Of(3 of 10) filters"
 
 
 class ClockSampler:
@@ -74,7 +92,7 @@ class ClockSampler:
                     self.samples.append([x.strip() for x in out.splitlines()[0].split(",")])
             except Exception:
                 pass
-            self.stop.wait(0.2)
+            self.stop.wait(0.1)
 
     def __enter__(self):
         self.thread = threading.Thread(target=self._run, daemon=True)
@@ -100,58 +118,69 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_sample(db, query, total_rows, budget_s=12.0):
-    """Oracle (CPU restatement of the reference's algorithm, faithful mode, all host threads) on a bounded sample of the
-    workload: the query restricted to one partition at a time, partitions taken in a fixed pseudo-random order (the cost
-    of a partition depends on how many of its rows the filter selects, so neither the smallest nor the largest are
-    representative), until about `budget_s` seconds of CPU work are spent or every partition was visited; scaled to the
-    whole database by rows: value = (sample_rows / total_rows) / seconds  [queries/s]."""
+def cpu_calibrate(db, query, budget_s=3.0):
+    """One full pass of the oracle (faithful mode = the reference's loops, all host threads) over every partition of this
+    process, one partition at a time, timed per partition. Returns (full_seconds, sample partitions, sample_seconds): the
+    sample is a prefix of a fixed pseudo-random order whose measured time reaches about budget_s."""
     sys.path.insert(0, str(ROOT / "tests"))
     import oracle_bind
     cores = os.cpu_count() or 1
     order = sorted(db.owned, key=lambda p: (p * 2654435761 + 12345) % (1 << 32))
-    sample, rows, seconds = [], 0, 0.0
+    times = {p: oracle_bind.time_query_subset(db, query, [p], faithful=True, threads=cores)[0] for p in order}
+    full = sum(times.values())
+    sample, t = [], 0.0
     for p in order:
-        t, _ = oracle_bind.time_query_subset(db, query, [p], faithful=True, threads=cores)
         sample.append(p)
-        rows += db.partition_rows(p)
-        seconds += t
-        if seconds >= budget_s:
+        t += times[p]
+        if t >= budget_s:
             break
-    what = "every partition" if rows == total_rows else f"{len(sample)} of {len(order)} partitions = {rows} of {total_rows} rows, scaled by rows"
-    return {"value": (rows / total_rows) / seconds, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"oracle faithful mode, one partition at a time in a fixed pseudo-random order, {what}, {seconds:.1f} s of CPU work"}, sample
+    return full, sample, t, cores
+
+
+def cpu_baseline_line(db, query, rows):
+    full, sample, t_sample, cores = cpu_calibrate(db, query)
+    return {"value": 1.0 / full, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle faithful mode (the reference's per-position loops), rotation query 0, ONE full pass over all {len(db.owned)} partitions of the {rows}-row database, "
+                      f"one partition at a time: {full:.1f} s of CPU work"}
 
 
 def run_reference(args, rank, world):
-    """The reference arm: the CPU restatement of the reference's own algorithm on the host cores."""
+    """The reference arm: the CPU restatement of the reference's own algorithm on the host cores (rank 0 only)."""
     if rank != 0:
         return
     import pysilo
-    t0 = time.time()
-    db = pysilo.Database.synthetic(args.rows, args.seed)
-    query = c3_query(db)
-    base, sample = cpu_sample(db, query, args.rows, budget_s=4.0)     # the per-step sample: about 4 s of CPU work
     sys.path.insert(0, str(ROOT / "tests"))
     import oracle_bind
-    cores = os.cpu_count() or 1
-    sample_rows = sum(db.partition_rows(p) for p in sample)
+    t0 = time.time()
+    db = pysilo.Database.synthetic(args.rows, args.seed)
+    query = rotation(db)[0]
+    full, sample, t_sample, cores = cpu_calibrate(db, query)
+    fraction = t_sample / full                       # measured share of the whole query's CPU time that the sample is
+    setup_s = time.time() - t0
+
     def one_step():
         return sum(oracle_bind.time_query_subset(db, query, [p], faithful=True, threads=cores)[0] for p in sample)
-    for _ in range(min(args.warmup, 1)):       # a CPU arm needs no more than one warm-up pass
+    for _ in range(min(args.warmup, 1)):            # a CPU arm needs no more than one warm-up pass
         one_step()
     times = [one_step() for _ in range(args.steps)]
     per_step = sum(times) / len(times)
-    value = (sample_rows / args.rows) / per_step
+    value = fraction / per_step                     # whole queries per second
+    sample_text = (f"oracle faithful mode (the reference's per-position loops), all {cores} host threads, rotation query 0; one full pass over all {len(db.owned)} partitions in set-up "
+                   f"took {full:.1f} s; each step = the query on {len(sample)} of {len(db.owned)} partitions = {fraction:.4f} of that time (measured); "
+                   f"value = fraction / step time; the reference itself is not buildable here (DESIGN.md 2)")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": per_step * 1e3 * args.rows / sample_rows, "higher_is_better": True, "scaling": "strong" if args.strong and args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "u32",
-            "data": "synthetic", "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt per shard, nucleotide Mutations under N-Of(3 of 10)", "rows": args.rows,
-                                            "note": "shard-queries/s of the host CPU: the same for any --gpus (the CPU answers the shards one after the other)"},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": base["sample"] + " per step; the reference itself is not buildable here (DESIGN.md 2)"},
+            "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 and not args.weak else "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": workload_name(args.rows), "rows": args.rows, "partitions": db.n_partitions, "sample_fraction_of_query": fraction, "full_pass_s": full,
+                       "note": "queries/s of the host CPU: the same for any --gpus"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_text},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "setup_s": round(time.time() - t0, 1)}
+            "setup_s": round(setup_s, 1)}
     print(json.dumps(line), flush=True)
+
+
+def table_digest(np, table):
+    valid = table[:VALID_ROWS * GENOME_LENGTH]
+    return {"sum": int(valid.astype(np.uint64).sum()), "crc32": zlib.crc32(valid.tobytes())}
 
 
 def main():
@@ -170,24 +199,23 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
     torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.init_process_group("nccl", device_id=device)
 
     t0 = time.time()
-    weak = world > 1 and not args.strong
-    units_per_step = world if weak else 1          # shard-queries per step (weak scaling: every rank answers the query on its own shard)
-    db = pysilo.Database.synthetic(args.rows, args.seed) if weak else pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank)
+    weak = world > 1 and args.weak
+    units_per_step = world if weak else 1          # weak: every rank answers the query on a shard of its own
+    db = pysilo.Database.synthetic(args.rows, args.seed + rank) if weak else pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank)
     total_rows = args.rows * (world if weak else 1)
     t_generate = time.time() - t0
     engine = pysilo.Engine(db, local_rank, db.owned)
     t_ingest = time.time() - t0 - t_generate
-    query = c3_query(db)
-    query_json = json.dumps(query)
-    query_bytes = query_json.encode()
+    queries = rotation(db)
+    texts = [json.dumps(q).encode() for q in queries]
     table_len = SIGMA * GENOME_LENGTH
-    counts = torch.zeros(table_len, dtype=torch.int32, device=f"cuda:{local_rank}")
-    prepared = pysilo.Prepared(engine, query)
+    root = rank == 0
 
     def barrier():
         torch.cuda.synchronize()
@@ -195,61 +223,91 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    if world > 1:      # the library sums the count tables over the ranks itself (ncclReduce to rank 0 on the stream of the count kernels)
-        id_t = torch.zeros(128, dtype=torch.uint8, device=counts.device)
-        if rank == 0:
+    def all_sum(values):
+        if world == 1:
+            return [int(v) for v in values]
+        t = torch.tensor(values, dtype=torch.int64, device=device)
+        dist.all_reduce(t)
+        return [int(v) for v in t.cpu()]
+
+    def all_max(values):
+        if world == 1:
+            return [float(v) for v in values]
+        t = torch.tensor(values, dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.cpu()]
+
+    # ---- before the communicator exists: every rank's LOCAL tables (valid-symbol rows), to check the reduced ones against ----
+    local_sums, alg_bytes, k1_bytes = [], [], []
+    for q in queries:
+        p = pysilo.Prepared(engine, q, use_graph=False)
+        p.run_device()
+        local_sums.append(table_digest(np, p.table(0, table_len))["sum"])
+        b = p.algorithmic_bytes(0)
+        alg_bytes.append(b["alg_bytes"])
+        k1_bytes.append(b["k1_bytes"])
+        p.close()
+    expected_sums = all_sum(local_sums)
+    local_k1_bytes = list(k1_bytes)
+    alg_bytes, k1_bytes = all_sum(alg_bytes), all_sum(k1_bytes)
+    if world > 1:      # the library sums the count tables over the ranks itself (ncclReduce to rank 0 inside the query's submission)
+        id_t = torch.zeros(128, dtype=torch.uint8, device=device)
+        if root:
             id_t.copy_(torch.frombuffer(bytearray(pysilo.comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(id_t, 0)
         pysilo.comm_init(engine, bytes(id_t.cpu().numpy().tobytes()), rank, world)
+    prepared = [pysilo.Prepared(engine, q, use_graph=(world == 1)) for q in queries]
 
-    def device_step():
-        prepared.run_device(0, counts.data_ptr(), table_len)      # synchronous; for N > 1 it ends with the NCCL reduce of the table to rank 0
+    def device_step(i):
+        return prepared[i % N_ROTATION].run_device()      # synchronous; for N > 1 it includes the NCCL reduce of the table to rank 0
 
-    def e2e_step():
+    def e2e_step(i):
         if world == 1:
-            return engine.execute_text(query_bytes)     # the JSON response text, as the reference's handler returns it
-        q = pysilo.DistributedQuery(engine, query_json)
-        q.local_table_device(0, counts.data_ptr(), table_len)      # local filter + count table, NCCL reduce to rank 0
-        result = None
-        if rank == 0:
-            q.set_table_device(0, counts.data_ptr())              # rows are selected on the device; only they come back
-            result = q.finish_text()                               # (a table of zeros -- no rank produced anything -- selects no row)
-        q.close()
-        return result
+            return engine.execute_text(texts[i % N_ROTATION])     # the JSON response text, as the reference's handler returns it
+        return engine.execute_sharded(texts[i % N_ROTATION], root)
 
-    for _ in range(max(args.warmup, 3)):
-        device_step()
-        e2e_step()
-    info = prepared.run_device(0, counts.data_ptr(), table_len, want_bytes=True)
-    local_k1_bytes = info["k1_bytes"]
-    if world > 1:
-        bytes_t = torch.tensor([info["alg_bytes"], info["k1_bytes"]], dtype=torch.int64, device=counts.device)
-        dist.all_reduce(bytes_t)
-        info["alg_bytes"], info["k1_bytes"] = int(bytes_t[0]), int(bytes_t[1])
+    warmup = max(args.warmup, N_ROTATION)
+    for i in range(warmup):
+        device_step(i)
+    # ---- the reduced tables: rank 0's table of every query against the sum of the ranks' local tables ----
+    digests = []
+    for k in range(N_ROTATION):
+        device_step(k)
+        if root:
+            d = table_digest(np, prepared[k].table(0, table_len))
+            assert d["sum"] == expected_sums[k], f"query {k}: reduced table sums to {d['sum']}, the ranks' local tables to {expected_sums[k]}"
+            digests.append(d)
 
     with ClockSampler(local_rank) as clocks:
-        # ---- value: device-resident steps, CUDA events on the library's stream, max over ranks ----
+        # ---- value: prepared queries, CUDA events around the timed steps, max over ranks ----
         barrier()
-        pysilo.k1_accumulated(engine, reset=True)
         launches0 = pysilo.launch_count(engine)
         pysilo.timer_begin(engine)
-        for _ in range(args.steps):
-            device_step()
+        result_rows = 0
+        for i in range(args.steps):
+            result_rows = device_step(i)
         device_ms = pysilo.timer_end(engine)
         barrier()
         launches = pysilo.launch_count(engine) - launches0
-        k1_ms, k1_launches = pysilo.k1_accumulated(engine, reset=True)
-        # ---- throughput with several queries in flight: host threads, one library lane (streams + scratch) each ----
+        # per query: CUDA-event time on the query's own stream, first kernel to last copy (median of 5 runs)
+        gpu_ms = []
+        for k in range(N_ROTATION):
+            samples = []
+            for _ in range(5):
+                device_step(k)
+                samples.append(prepared[k].elapsed_ms())
+            gpu_ms.append(statistics.median(samples))
+        gpu_ms = all_max(gpu_ms)
+        # ---- throughput with several queries in flight: one host thread per prepared query ----
         throughput = None
         if world == 1 and args.in_flight > 1:
-            q_threads = args.in_flight
+            q_threads = min(args.in_flight, N_ROTATION)
             per_thread = max(25, (16 * args.steps + q_threads - 1) // q_threads)
-            tables = [torch.zeros(table_len, dtype=torch.int32, device=counts.device) for _ in range(q_threads)]
 
             def concurrent(work):
                 start = threading.Barrier(q_threads + 1)
                 def loop(k):
-                    work(k)                                   # binds the thread to its lane, grows the lane's buffers
+                    work(k)
                     start.wait()
                     for _ in range(per_thread):
                         work(k)
@@ -265,88 +323,143 @@ def main():
                 ms = pysilo.timer_end(engine)                  # every call is synchronous: all GPU work is done here
                 return q_threads * per_thread / (ms * 1e-3), q_threads * per_thread / (time.perf_counter() - w)
 
-            dev_qps, _ = concurrent(lambda k: prepared.run_device(0, tables[k].data_ptr(), table_len))
-            _, e2e_qps = concurrent(lambda k: engine.execute_text(query_bytes))
+            dev_qps, _ = concurrent(lambda k: prepared[k].run_device())
+            engine.set_plan_cache(False)
+            _, e2e_qps = concurrent(lambda k: engine.execute_text(texts[k]))
             throughput = {"queries_in_flight": q_threads, "queries": q_threads * per_thread, "value": dev_qps, "e2e_value": e2e_qps, "unit": UNIT,
-                          "how": "host threads calling the same entry points concurrently; device-resident replay timed with CUDA events, e2e by wall clock"}
-        # ---- the container scan timed alone (kernels of a query serialised on one stream): the roofline line ----
+                          "how": "one host thread per rotation query calling the same entry points concurrently; prepared replay timed with CUDA events, e2e (plan cache off) by wall clock"}
+        # ---- the container scan timed alone (kernels of a query serialised on one stream): the roofline line, rotation query 0 ----
+        engine.set_plan_cache(False)
         pysilo.set_overlap(engine, False)
-        for _ in range(2):
-            device_step()
+        for _ in range(3):
+            e2e_step(0)
         pysilo.k1_accumulated(engine, reset=True)
-        for _ in range(args.steps):
-            device_step()
+        for _ in range(max(args.steps // 2, 10)):
+            e2e_step(0)
         k1_alone_ms, k1_alone_launches = pysilo.k1_accumulated(engine, reset=True)
         pysilo.set_overlap(engine, True)
+        for _ in range(3):
+            e2e_step(0)
+        pysilo.k1_accumulated(engine, reset=True)
+        for _ in range(max(args.steps // 2, 10)):
+            e2e_step(0)
+        k1_ms, k1_launches = pysilo.k1_accumulated(engine, reset=True)
         barrier()
-        # ---- e2e: public API with host buffers, wall clock bracketed by barrier + synchronize ----
+        # ---- e2e: public call with host buffers, plan cache off, wall clock bracketed by barrier + synchronize ----
+        for i in range(N_ROTATION):
+            e2e_step(i)
         h2d0, d2h0 = pysilo.transfer_bytes(engine)
         barrier()
         w0 = time.perf_counter()
-        for _ in range(args.steps):
-            result = e2e_step()
+        for i in range(args.steps):
+            result = e2e_step(i)
         barrier()
         e2e_s = time.perf_counter() - w0
         h2d1, d2h1 = pysilo.transfer_bytes(engine)
+        # ---- the same with the engine's plan cache (query text -> prepared query; a CUDA graph at N = 1) ----
+        e2e_cached_s = None
+        if world == 1:
+            engine.set_plan_cache(True)
+            for i in range(3 * N_ROTATION):
+                e2e_step(i)
+            barrier()
+            w0 = time.perf_counter()
+            for i in range(args.steps):
+                result = e2e_step(i)
+            barrier()
+            e2e_cached_s = time.perf_counter() - w0
+    device_ms, e2e_s = all_max([device_ms, e2e_s])
+    # roofline line: the rank whose container scan of query 0 has the most bytes (a rank may own no selected partition at all)
+    roofline_rank = 0
+    mine = [float(local_k1_bytes[0]), k1_ms, float(k1_launches), k1_alone_ms, float(k1_alone_launches)]
     if world > 1:
-        t = torch.tensor([device_ms, e2e_s], dtype=torch.float64, device=counts.device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        device_ms, e2e_s = float(t[0]), float(t[1])
-        # roofline line: the rank whose container scan has the most bytes (rank 0 may own no selected partition at all)
-        mine = torch.tensor([float(local_k1_bytes), k1_ms, float(k1_launches), k1_alone_ms, float(k1_alone_launches)], dtype=torch.float64, device=counts.device)
-        every = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(every, mine)
-        best = max(range(world), key=lambda r: float(every[r][0]))
-        local_k1_bytes, k1_ms, k1_launches, k1_alone_ms, k1_alone_launches = (float(x) for x in every[best])
-        local_k1_bytes, roofline_rank = int(local_k1_bytes), best
-    else:
-        roofline_rank = 0
+        t = torch.tensor(mine, dtype=torch.float64, device=device)
+        every = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(every, t)
+        roofline_rank = max(range(world), key=lambda r: float(every[r][0]))
+        mine = [float(x) for x in every[roofline_rank].cpu()]
+    scan_bytes, k1_ms, k1_launches, k1_alone_ms, k1_alone_launches = mine
 
-    if rank == 0:
+    extra = None
+    if args.lineage and world == 1:
+        extra = lineage_queries(pysilo, db, engine)
+
+    if root:
         peak, peak_source = measured_peak()
-        k1_instep_ms = k1_ms / max(k1_launches, 1)          # inside the timed steps: the missing-symbol kernel runs beside it
+        k1_instep_ms = k1_ms / max(k1_launches, 1)          # with the missing-symbol kernel beside it
         k1_avg_ms = k1_alone_ms / max(k1_alone_launches, 1)  # the same launches with nothing beside them
-        achieved = local_k1_bytes / (k1_avg_ms * 1e-3) / 1e9 if k1_avg_ms > 0 else 0.0
+        achieved = scan_bytes / (k1_avg_ms * 1e-3) / 1e9 if k1_avg_ms > 0 else 0.0
         traffic = None
         traffic_file = ROOT / "profiles" / "k1_traffic.json"
-        if traffic_file.exists():
-            traffic = json.loads(traffic_file.read_text()).get(str(args.rows)) if world == 1 else None
+        if traffic_file.exists() and world == 1:
+            traffic = json.loads(traffic_file.read_text()).get(str(args.rows))
         stats = pysilo.pool_stats(engine)
-        d2h_extra = 0
+        ms_per_step = device_ms / args.steps
+        mean_alg = sum(alg_bytes) / len(alg_bytes)
+        mean_gpu_ms = sum(gpu_ms) / len(gpu_ms)
         line = {
-            "metric": METRIC, "value": units_per_step * args.steps / (device_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": device_ms / args.steps, "higher_is_better": True, "scaling": "weak" if weak or world == 1 else "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": f"C3: {args.rows} synthetic sequences x {GENOME_LENGTH} nt per shard, nucleotide Mutations under N-Of(3 of 10)", "rows": total_rows,
-                       "rows_per_rank": args.rows if weak or world == 1 else None, "shard_queries_per_step": units_per_step,
-                       "partitions": db.n_partitions * (world if weak else 1), "partitions_on_rank0": len(db.owned), "l2": "inputs larger than L2 (container pool streamed once per query)",
-                       "parallelism": (f"{world} shard(s) of {args.rows} sequences, one per GPU (DatabasePartitions are the unit of sharding); a step = the query on every shard + NCCL reduce "
-                                       f"of the count tables; value = shard-queries/s" if weak or world == 1 else f"one database of {args.rows} sequences, partitions sharded over {world} GPUs, NCCL reduce of the count table")},
-            "e2e": {"value": units_per_step * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps + len(query_json),
-                    "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps + d2h_extra, "ms_per_step": e2e_s * 1e3 / args.steps},
+            "metric": METRIC, "value": units_per_step * args.steps / (device_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak" if weak or world == 1 else "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": workload_name(args.rows), "rows": total_rows, "partitions": db.n_partitions * (world if weak else 1), "partitions_on_rank0": len(db.owned),
+                       "l2": "inputs larger than L2 (container pool streamed once per query; 8 different queries in rotation)",
+                       "parallelism": (f"{world} replicated shard(s) of {args.rows} sequences (seed + rank), one per GPU" if weak else
+                                       f"one database of {args.rows} sequences, DatabasePartitions sharded over {world} GPU(s), NCCL reduce of the valid-symbol rows of the count table inside the query's submission")},
+            "e2e": {"value": units_per_step * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps + sum(len(t) for t in texts) // len(texts),
+                    "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps, "ms_per_step": e2e_s * 1e3 / args.steps, "plan_cache": "off",
+                    "cached": {"value": args.steps / e2e_cached_s, "ms_per_step": e2e_cached_s * 1e3 / args.steps, "note": "query text -> prepared query (CUDA graph) in the engine's plan cache"} if e2e_cached_s else None},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k1_and_popcount", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "peak_source": peak_source, "rank": roofline_rank, "algorithmic_bytes_per_launch": local_k1_bytes, "avg_launch_ms": k1_avg_ms,
-                         "avg_launch_ms_overlapped": k1_instep_ms, "achieved_overlapped": local_k1_bytes / (k1_instep_ms * 1e-3) / 1e9 if k1_instep_ms > 0 else 0.0,
-                         "timing": "CUDA events around the launch on the library stream; avg_launch_ms with the query's kernels serialised (sb_set_overlap 0), _overlapped as they run in the timed steps",
-                         "share_of_step": k1_instep_ms / (device_ms / args.steps) if device_ms else None},
+            "roofline": {"bound": "hbm", "kernel": "k1_scan", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "peak_source": peak_source, "rank": roofline_rank, "query": 0, "algorithmic_bytes_per_launch": scan_bytes, "avg_launch_ms": k1_avg_ms,
+                         "avg_launch_ms_overlapped": k1_instep_ms, "achieved_overlapped": scan_bytes / (k1_instep_ms * 1e-3) / 1e9 if k1_instep_ms > 0 else 0.0,
+                         "timing": "CUDA events around the launch on the library stream (one-shot entry point); avg_launch_ms with the query's kernels serialised (sb_set_overlap 0), _overlapped with the missing-symbol kernel beside it",
+                         "share_of_query": k1_instep_ms / gpu_ms[0] if gpu_ms[0] else None},
+            "query_gpu_ms": gpu_ms, "query_algorithmic_bytes": alg_bytes, "query_k1_bytes": k1_bytes,
+            "scan_gb_per_s": mean_alg / (mean_gpu_ms * 1e-3) / 1e9 if mean_gpu_ms else None,
+            "scan_note": "mean algorithmic bytes of the rotation's queries / mean CUDA-event time of a query on its own stream (first kernel to last copy; N > 1: slowest rank)",
+            "table_digests": digests, "table_check": "rank 0's (reduced) table of every query sums to the sum of the ranks' local tables over the valid-symbol rows",
             "throughput": throughput,
-            "scan_gb_per_s": info["alg_bytes"] / (device_ms / args.steps * 1e-3) / 1e9,
-            "algorithmic_bytes_per_query": info["alg_bytes"],
             "clocks": clocks.summary(),
             "pool": {k: stats[k] for k in ("array_containers", "run_containers", "bitset_containers", "payload_bytes", "directory_bytes", "missing_bytes", "full_table_bytes", "n_work_items")},
-            "result_rows": (result.count('"mutation"') if isinstance(result, str) else len(result)) if result is not None else None,
+            "result_rows": int(result_rows),
+            "other_queries": extra,
             "setup_s": {"generate": round(t_generate, 1), "ingest": round(t_ingest, 1)},
         }
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"], _ = cpu_sample(db, query, args.rows)
+            line["cpu_baseline"] = cpu_baseline_line(db, queries[0], args.rows)
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line), flush=True)
-    prepared.close()
+    for p in prepared:
+        p.close()
     if world > 1:
         pysilo.comm_free(engine)
         dist.barrier()
         dist.destroy_process_group()
+
+
+def lineage_queries(pysilo, db, engine):
+    """C5's other two filters: a lineage with sublineages (full / partial / empty partitions) and True (all full)"""
+    names = sorted({".".join(n.split(".")[:k]) for n in db.lineage_names() for k in range(1, n.count(".") + 2)}, key=lambda n: (n.count("."), n))
+    out = []
+    for label, flt in [(f"PangoLineage {names[len(names) // 3]}*", {"type": "PangoLineage", "column": "pangoLineage", "value": names[len(names) // 3], "includeSublineages": True}),
+                       (f"PangoLineage {names[2]}*", {"type": "PangoLineage", "column": "pangoLineage", "value": names[2], "includeSublineages": True}), ("True", {"type": "True"})]:
+        q = {"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": flt}
+        p = pysilo.Prepared(engine, q)
+        samples = []
+        for _ in range(8):
+            rows = p.run_device()
+            samples.append(p.elapsed_ms())
+        text = json.dumps(q).encode()
+        engine.set_plan_cache(False)
+        for _ in range(3):
+            engine.execute_text(text)
+        w = time.perf_counter()
+        for _ in range(10):
+            engine.execute_text(text)
+        out.append({"filter": label, "gpu_ms": statistics.median(samples), "e2e_ms": (time.perf_counter() - w) * 100, "result_rows": rows, "algorithmic_bytes": p.algorithmic_bytes(0)["alg_bytes"],
+                    "note": "full partitions are table hits (precomputed at load): their algorithmic bytes are not read"})
+        p.close()
+    return out
 
 
 if __name__ == "__main__":

@@ -192,6 +192,8 @@ int sb_query_prepare(sb_db* db, uint32_t n, const uint32_t* partitions, const sb
 int sb_query_run(sb_query* q, sb_sequence_rows* out, uint64_t* cardinalities);
 /* the uint32[n_symbols][length] table of sequence `index` of the last run, in device memory (valid until the next run) */
 int sb_query_table_device(sb_query* q, uint32_t index, const void** device_counts, size_t* counts_len);
+/* CUDA-event time of the last sb_query_run, recorded on the query's own stream: first kernel to last copy */
+int sb_query_elapsed_ms(sb_query* q, float* ms);
 int sb_query_free(sb_query* q);
 /* synchronous copy out of device memory the library handed out (sb_query_table_device) */
 int sb_copy_from_device(void* host, const void* device, size_t bytes);

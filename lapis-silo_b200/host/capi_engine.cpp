@@ -252,6 +252,12 @@ int silo_prepared_bytes(void* engine_, void* prepared_, uint32_t name_index, uin
                                                    filters.results.data(), alg_bytes, k1_bytes));
    });
 }
+float silo_prepared_elapsed_ms(void* prepared_) {
+   auto& p = *static_cast<DeviceDatabase::PreparedQuery*>(prepared_);
+   float ms = 0;
+   if (p.handle) sb_query_elapsed_ms(p.handle, &ms);
+   return ms;
+}
 void silo_engine_set_plan_cache(void* engine_, int enabled) { static_cast<DeviceDatabase*>(engine_)->setPlanCache(enabled != 0); }
 
 // Multi-GPU (one process per GPU, sb_comm_init done): every rank calls with the same query text in the same order; the

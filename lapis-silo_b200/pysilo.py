@@ -70,6 +70,7 @@ def host():
         "silo_prepared_run": (vp, [vp, vp]),
         "silo_prepared_table": (ctypes.c_int, [vp, u32, vp, u64]),
         "silo_prepared_bytes": (ctypes.c_int, [vp, vp, u32, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
+        "silo_prepared_elapsed_ms": (ctypes.c_float, [vp]),
         "silo_engine_set_plan_cache": (None, [vp, ctypes.c_int]),
         "silo_engine_execute_sharded": (vp, [vp, cp, ctypes.c_int]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32]),
@@ -435,6 +436,10 @@ class Prepared:
         if host().silo_prepared_run_device(self.engine.handle, self.handle, ctypes.byref(n)) != 0:
             raise _error()
         return n.value
+
+    def elapsed_ms(self):
+        """CUDA-event time of the last run on the query's own stream (first kernel to last copy)"""
+        return host().silo_prepared_elapsed_ms(self.handle)
 
     def run_text(self):
         return _take_string(host().silo_prepared_run(self.engine.handle, self.handle))
