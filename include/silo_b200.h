@@ -161,6 +161,17 @@ int sb_sequence_set_reference(sb_db* db, const char* store_name, const uint8_t* 
 /* rows of a count table that already is in device memory (e.g. after an NCCL reduce) */
 int sb_mutation_rows_from_table(sb_db* db, const char* store_name, const void* device_counts, double min_proportion,
                                 const uint8_t* valid, uint32_t n_valid, sb_mutation_row* rows, size_t capacity, size_t* n_rows);
+/* sb_mutation_rows_from_table for callers that cannot reach cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid allocation). No counterpart in the reference.
+ * Same arguments, same rows in the same order; the kernel's scratch (row counter + row area) is a file-scope device array
+ * of 4 MiB that every GPU holds from the moment it loads the library until exit, so the call allocates nothing -- no
+ * cudaMalloc / cudaFree / cudaMallocHost, no growth of a library buffer; the rows are copied straight into `rows`.
+ * Limit: length * n_valid <= SB_STATIC_MAX_ROWS (nucleotides: 29,903 * 5 = 149,515), otherwise the call fails with a
+ * message that says so. All calls share the one array: calls that overlap on a GPU would race on it; within a process
+ * the library serialises them with a mutex. */
+#define SB_STATIC_MAX_ROWS 262128u
+int sb_mutation_rows_from_table_static(sb_db* db, const char* store_name, const void* device_counts, double min_proportion,
+                                       const uint8_t* valid, uint32_t n_valid, sb_mutation_row* rows, size_t capacity, size_t* n_rows);
 /* sb_mutations + the selection in one call with one synchronisation; *n_rows may exceed capacity (then call again) */
 int sb_mutations_rows(sb_db* db, const char* store_name, uint32_t n, const uint32_t* partitions, sb_result* const* results,
                       double min_proportion, const uint8_t* valid, uint32_t n_valid,

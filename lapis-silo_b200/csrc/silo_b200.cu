@@ -398,6 +398,73 @@ int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, 
 #include "api_action.inc"
 #include "api_query.inc"
 
+// ---- row selection without any allocation ------------------------------------------------------------------------------
+// For callers that must not reach cudaMalloc (graph capture around them, tight serving loops, harnesses that forbid it):
+// sb_mutation_rows_from_table with the scratch of k4_select_rows -- the row counter and the row area -- in a file-scope
+// device array instead of the lane's growable buffer. Every GPU that loads the library holds the array (4 MiB) until exit.
+// All calls share it and it keeps the last call's contents: the counter is cleared on the stream before every launch, the
+// row area needs no clearing (only the first `counter` rows are read back). Two calls that overlap on one GPU would race
+// on it; inside one process the mutex below serialises them.
+namespace sb {
+constexpr size_t STATIC_SCRATCH_BYTES = size_t(4) << 20;
+constexpr size_t STATIC_HEADER_BYTES = 256;      // [0] row counter; the rows start 256-byte aligned behind it
+constexpr size_t STATIC_MAX_ROWS = (STATIC_SCRATCH_BYTES - STATIC_HEADER_BYTES) / sizeof(sb_mutation_row);
+static_assert(STATIC_MAX_ROWS == SB_STATIC_MAX_ROWS, "include/silo_b200.h states the limit");
+static __device__ __align__(256) uint8_t g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// In host code g_static_scratch is only the symbol's host-side stand-in: the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+static std::mutex g_static_mutex;
+static uint8_t* g_static_ptr[STATIC_MAX_DEVICES] = {};
+inline uint8_t* staticScratchOfCurrentDevice(int device) {      // g_static_mutex held
+   SB_REQUIRE(device >= 0 && device < STATIC_MAX_DEVICES, "device index beyond the static scratch table");
+   if (!g_static_ptr[device]) {
+      void* p = nullptr;
+      SB_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+      SB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned no address for the static scratch");
+      g_static_ptr[device] = static_cast<uint8_t*>(p);
+   }
+   return g_static_ptr[device];
+}
+}  // namespace sb
+
+extern "C" int sb_mutation_rows_from_table_static(sb_db* db, const char* store_name, const void* device_counts, double min_proportion,
+                                                  const uint8_t* valid, uint32_t n_valid, sb_mutation_row* rows, size_t capacity, size_t* n_rows) {
+   return guarded([&] {
+      SB_REQUIRE(db && db->finalized, "sb_mutation_rows_from_table_static before sb_db_finalize");
+      SB_REQUIRE(device_counts && n_rows && (rows || capacity == 0), "null argument");
+      sb_lane* ln = laneOf(db);
+      std::lock_guard<std::mutex> lock(ln->mutex);
+      useDevice(db);
+      Sequence& seq = findSequence(db, store_name);
+      const RowSelection rs = makeRowSelection(seq, min_proportion, valid, n_valid);
+      const size_t max_rows = size_t(seq.length) * n_valid;      // what k4_select_rows can emit
+      SB_REQUIRE(max_rows <= STATIC_MAX_ROWS, "sb_mutation_rows_from_table_static: length * n_valid = " + std::to_string(max_rows) + " rows exceed the static scratch (" +
+                                                 std::to_string(STATIC_MAX_ROWS) + " rows); use sb_mutation_rows_from_table");
+      std::lock_guard<std::mutex> scratch_lock(g_static_mutex);
+      uint8_t* scratch = staticScratchOfCurrentDevice(db->device);
+      uint32_t* d_counter = reinterpret_cast<uint32_t*>(scratch);
+      sb_mutation_row* d_rows = reinterpret_cast<sb_mutation_row*>(scratch + STATIC_HEADER_BYTES);
+      SB_CUDA(cudaMemsetAsync(d_counter, 0, 16, ln->stream));
+      k4_select_rows<<<(seq.length + 255) / 256, 256, 0, ln->stream>>>(static_cast<const uint32_t*>(device_counts), seq.length, seq.reference.ptr, rs.valid, rs.min_proportion,
+                                                                       d_rows, uint32_t(max_rows), d_counter);
+      SB_CUDA(cudaGetLastError());
+      db->launch_count += 1;
+      uint32_t n = 0;      // results go straight into the caller's memory: no staging buffer of the library is grown
+      SB_CUDA(cudaMemcpyAsync(&n, d_counter, 4, cudaMemcpyDeviceToHost, ln->stream));
+      SB_CUDA(cudaStreamSynchronize(ln->stream));
+      *n_rows = n;
+      db->d2h_bytes += 4;
+      if (n == 0 || n > capacity) return;
+      SB_CUDA(cudaMemcpyAsync(rows, d_rows, size_t(n) * sizeof(sb_mutation_row), cudaMemcpyDeviceToHost, ln->stream));
+      SB_CUDA(cudaStreamSynchronize(ln->stream));
+      db->d2h_bytes += size_t(n) * sizeof(sb_mutation_row);
+      std::sort(rows, rows + n, [](const sb_mutation_row& a, const sb_mutation_row& b) { return a.position != b.position ? a.position < b.position : a.symbol < b.symbol; });
+      for (size_t i = 0; i < n; ++i) rows[i].symbol = valid[rows[i].symbol];
+   });
+}
+
 #ifdef SB_K1_TIMELINE
 // diagnostics build (tools/k1_experiment.py): per-CTA time stamps of the container scan
 extern "C" int sb_debug_timeline_enable(uint32_t max_blocks) {
