@@ -134,14 +134,36 @@ def cpu_calibrate(db, query, budget_s=3.0):
         t += times[p]
         if t >= budget_s:
             break
-    return full, sample, t, cores
+    return full, sample, t, cores, times
 
 
-def cpu_baseline_line(db, query, rows):
-    full, sample, t_sample, cores = cpu_calibrate(db, query)
-    return {"value": 1.0 / full, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"oracle faithful mode (the reference's per-position loops), rotation query 0, ONE full pass over all {len(db.owned)} partitions of the {rows}-row database, "
-                      f"one partition at a time: {full:.1f} s of CPU work"}
+def cpu_baseline_line(db, query, rows, budget_s=20.0):
+    """The in-line CPU baseline of the default run: a BOUNDED sample (about budget_s of CPU work) of the same query. The
+    reference's Mutations loop costs O(|F_p| * L) per partition (mutations.cpp:74-83: one contains() per filtered row and
+    position), so the sample -- partitions in a fixed pseudo-random order until the budget is spent -- is scaled to the whole
+    query by FILTERED rows, not by rows (a partition the filter does not select costs nothing). `--impl reference` measures
+    the full pass and prints per-partition times next to the filtered rows, so the estimator can be checked."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_bind
+    cores = os.cpu_count() or 1
+    flt = query["filterExpression"]
+    filtered = {p: oracle_bind.filter_cardinality(db, flt, p) for p in db.owned}
+    total_filtered = sum(filtered.values())
+    order = sorted((p for p in db.owned if filtered[p]), key=lambda p: (p * 2654435761 + 12345) % (1 << 32))
+    sample, t, seen = [], 0.0, 0
+    for p in order:
+        t += oracle_bind.time_query_subset(db, query, [p], faithful=True, threads=cores)[0]
+        seen += filtered[p]
+        sample.append(p)
+        if t >= budget_s:
+            break
+    full = t * total_filtered / max(seen, 1)
+    fast_s = oracle_bind.time_query_subset(db, query, list(db.owned), faithful=False, threads=cores)[0]
+    return {"value": 1.0 / full if full else None, "unit": UNIT, "cores": cores, "kind": "port",
+            "best_cpu_algorithm": {"value": 1.0 / fast_s if fast_s else None, "unit": UNIT, "seconds": fast_s,
+                                   "note": "NOT the reference's algorithm: the oracle's fast mode (difference array instead of the O(|F| L) contains() loop), whole query, all host threads"},
+            "sample": f"oracle faithful mode (the reference's per-position loops, all {cores} host threads), rotation query 0 on {len(sample)} of the {len(order)} partitions the filter selects "
+                      f"({seen} of {total_filtered} filtered rows, {t:.1f} s of CPU work), scaled by filtered rows to {full:.1f} s for the whole {rows}-row query"}
 
 
 def run_reference(args, rank, world):
@@ -154,8 +176,9 @@ def run_reference(args, rank, world):
     t0 = time.time()
     db = pysilo.Database.synthetic(args.rows, args.seed)
     query = rotation(db)[0]
-    full, sample, t_sample, cores = cpu_calibrate(db, query)
+    full, sample, t_sample, cores, per_partition = cpu_calibrate(db, query)
     fraction = t_sample / full                       # measured share of the whole query's CPU time that the sample is
+    filtered = {p: oracle_bind.filter_cardinality(db, query["filterExpression"], p) for p in db.owned}
     setup_s = time.time() - t0
 
     def one_step():
@@ -171,6 +194,7 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 and not args.weak else "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": workload_name(args.rows), "rows": args.rows, "partitions": db.n_partitions, "sample_fraction_of_query": fraction, "full_pass_s": full,
+                       "per_partition": [{"partition": p, "rows": db.partition_rows(p), "filtered_rows": filtered[p], "cpu_s": round(per_partition[p], 3)} for p in db.owned],
                        "note": "queries/s of the host CPU: the same for any --gpus"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_text},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

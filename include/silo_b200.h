@@ -139,8 +139,11 @@ int sb_mutations(sb_db* db, const char* store_name, uint32_t n, const uint32_t* 
  * process that also uses PyTorch imports torch first, so that the one libnccl.so.2 of the process is torch's.
  *   sb_comm_unique_id   rank 0: a fresh ncclUniqueId (128 bytes) for the caller to hand to every rank
  *   sb_comm_init        every rank: joins the communicator on the db's device. From then on sb_mutations_device leaves the
- *                       SUM over all ranks in rank 0's buffer (other ranks: their local table), and every rank must call
- *                       it for the same sequence in the same order (collective), one query at a time.
+ *                       SUM over all ranks in rank 0's buffer (other ranks: their local table). Calls that reduce
+ *                       (sb_mutations_device, sb_query_mutations, sb_query_run) are then COLLECTIVE: every rank must issue them
+ *                       for the same query in the same order. Inside a rank the library runs one collective call at a time
+ *                       (the reduces of two host threads never interleave); agreeing on the order across ranks is the
+ *                       caller's job -- with several request threads, e.g. a sequence number handed out by rank 0.
  *   sb_comm_free        leaves the communicator (sb_db_free does it too). */
 int sb_comm_unique_id(void* id_128_bytes);
 int sb_comm_init(sb_db* db, const void* id_128_bytes, int rank, int world_size);
@@ -186,7 +189,7 @@ int sb_mutations_rows(sb_db* db, const char* store_name, uint32_t n, const uint3
  * out[k] belongs to sequence_names[k]: the caller provides rows / capacity; n_rows may exceed capacity (then call again
  * with a larger buffer); produced == 0 mirrors preFilterBitmaps yielding no entry for the sequence (mutations.cpp:36-63).
  * cardinalities (optional) receives |F_p| per listed partition.
- * With sb_comm_init active every rank calls with its own partitions, in the same order on all ranks (sb_comm_enter); the
+ * With sb_comm_init active every rank calls with its own partitions, in the same order on all ranks (see sb_comm_init); the
  * tables are summed over the ranks before the selection and only rank 0 receives rows. */
 typedef struct sb_sequence_rows { sb_mutation_row* rows; size_t capacity; size_t n_rows; int produced; int pad; } sb_sequence_rows;
 int sb_query_mutations(sb_db* db, uint32_t n, const uint32_t* partitions, const sb_node* const* plans, const uint32_t* n_nodes,
@@ -211,6 +214,21 @@ int sb_copy_from_device(void* host, const void* device, size_t bytes);
 
 /* aggregateWithoutGrouping (aggregated.cpp:58-66): sum of cardinalities, uint32 wrap-around. */
 int sb_aggregated_count(sb_db* db, uint32_t n, sb_result* const* results, uint32_t* count);
+
+/* Aggregated with groupByFields (Aggregated::execute, aggregated.cpp:91-149; tuples: actions/tuple.cpp:29-76). The host
+ * dictionary-codes every group-by column once (code = index of the row's value among the column's distinct values, the same
+ * dictionary for all partitions) and registers the codes per partition:
+ *   sb_group_column_add   uint32 codes[n] of one column of one partition; allowed after sb_db_finalize (a column is coded
+ *                         when a query first groups by it)
+ *   sb_aggregated_grouped counts the filtered rows of the n listed partitions per tuple. group_column_ids[i * n_columns + c]
+ *                         is column c of partitions[i]; cardinalities[c] bounds the codes of column c. A tuple comes back as
+ *                         the mixed-radix key ((code_0 * cardinalities[1] + code_1) * cardinalities[2] + code_2) ...; rows
+ *                         are sorted by key (the reference's order is that of its hash map and is fixed by orderByFields);
+ *                         *n_rows may exceed capacity (then call again). count is uint32 like the reference's map values. */
+typedef struct sb_group_row { uint64_t key; uint32_t count; uint32_t pad; } sb_group_row;
+int sb_group_column_add(sb_db* db, uint32_t partition, const uint32_t* codes, uint32_t n, uint32_t* group_column_id);
+int sb_aggregated_grouped(sb_db* db, uint32_t n, const uint32_t* partitions, sb_result* const* results, uint32_t n_columns,
+                          const uint32_t* group_column_ids, const uint32_t* cardinalities, sb_group_row* rows, size_t capacity, size_t* n_rows);
 
 /* ---- introspection (mirrors /info?details=true, database.cpp:239-305) -------------------------- */
 typedef struct sb_pool_stats {
@@ -239,6 +257,8 @@ int sb_transfer_bytes(const sb_db* db, uint64_t* h2d, uint64_t* d2h);
  * the missing-symbol kernel beside the container scan). enabled = 0 serialises them on one stream, which is
  * how bench.py times the container scan alone for its roofline line. */
 int sb_set_overlap(sb_db* db, int enabled);
+/* Tuning: which compiled shape of the container scan runs (0 = default); tools/ measure them side by side in one process. */
+int sb_debug_set_k1_variant(sb_db* db, uint32_t variant);
 /* Accumulated CUDA-event time of the container scan (k1_scan) since the last call with reset != 0, and its launch count
  * (one-shot entry points only: a graph replay records no events). */
 int sb_k1_accumulated(sb_db* db, int reset, double* total_ms, uint64_t* launches);

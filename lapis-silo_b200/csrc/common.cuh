@@ -69,7 +69,8 @@ int guarded(F&& f) {
 // A segment's postings start 16-byte aligned; the gap is filled with postings of the dummy slot
 // `tile_slots` (never flushed), so the scan needs no tail handling.
 enum : uint32_t { KIND_ARRAY = 0, KIND_BITSET = 1, KIND_RUN = 2, KIND_NULL = 3 };
-constexpr uint32_t TILE_POSITIONS = 256;     // positions per tile (shared-memory count table = 256 * Sigma words)
+constexpr uint32_t TILE_POSITIONS = 256;     // positions per tile (shared-memory count table = 256 * Sigma words); SB_TILE_POSITIONS: tuning
+constexpr uint32_t MAX_TILE_POSITIONS = 512;
 constexpr uint32_t SLAB_KEYS = 4;            // container keys per slab
 constexpr uint32_t SLAB_WORDS32 = SLAB_KEYS * 2048;   // 32-bit filter words per slab (32 KB)
 constexpr uint32_t FLAT_MAX = 16;            // containers up to this cardinality become postings
@@ -79,11 +80,12 @@ constexpr uint32_t POSTING_ROW_MASK = (1u << POSTING_ROW_BITS) - 1u;
 struct LargeEntry {
    uint32_t offset16;        // payload offset in the large pool, 16-byte units
    uint32_t size;            // array: cardinality, run: number of runs, bitset: cardinality (unused by the scan)
-   uint32_t where;           // slot':14 | kind:2 << 14 | key_local:2 << 16
-   uint32_t pad;
+   uint32_t where;           // slot':14 | kind:2 << 14 | key_local:2 << 16 | tile:14 << 18
+   uint32_t slab;            // the (tile, slab) segment it belongs to: a unit of the large-container scan finds its partition by itself
    __host__ __device__ inline uint32_t slot() const { return where & 0x3FFFu; }
    __host__ __device__ inline uint32_t kind() const { return (where >> 14) & 3u; }
    __host__ __device__ inline uint32_t keyLocal() const { return (where >> 16) & 3u; }
+   __host__ __device__ inline uint32_t tile() const { return where >> 18; }
 };
 static_assert(sizeof(LargeEntry) == 16, "LargeEntry must be 16 bytes");
 
@@ -95,6 +97,14 @@ struct WorkItem {            // one unit of the Mutations scan: a weight-bounded
    uint32_t partition, key0;          // of the slab (saves the scan a dependent load)
 };
 static_assert(sizeof(WorkItem) == 32, "WorkItem must be 32 bytes");
+
+// What a CTA of the scan takes from the hand-out counter: consecutive work items (ascending tile) of ONE slab, so that the
+// 32 KB filter slice of the slab is copied into shared memory once per run instead of once per item.
+struct RunRec {
+   uint32_t first_item, n_items;      // items [first_item, first_item + n_items) of SeqDev::items
+   uint32_t partition, weight_kb;
+};
+static_assert(sizeof(RunRec) == 16, "RunRec must be 16 bytes");
 
 struct SlabRec {
    uint32_t partition;       // db-local partition index
@@ -129,8 +139,8 @@ struct PartInput {
 };
 // Per-(query, sequence) header the classification leaves for the count kernels.
 struct ActionHead {
-   uint32_t n_partial, n_full, produced, n_selected;   // n_selected: work items of the partial partitions (compact_items)
-   uint32_t next_item, pad0;                           // hand-out counter of the container scan
+   uint32_t n_partial, n_full, produced, n_selected;   // n_selected: runs of work items of the partial partitions (compact_runs)
+   uint32_t next_run, pad0;                            // hand-out counter of the container scan
    uint64_t k2_total_cost;
 };
 
@@ -138,7 +148,8 @@ struct ActionHead {
 struct SeqDev {
    const uint32_t* postings;
    const LargeEntry* large_entries;
-   const WorkItem* items;       // heaviest first over all partitions (the scan hands them out in this order)
+   const WorkItem* items;       // ordered by (slab, tile): the items of a run are consecutive
+   const RunRec* runs;          // heaviest first over all partitions (the scan hands them out in this order)
    const SegRec* segs;          // [n_tiles * n_slabs + 1]
    const SlabRec* slabs;        // [n_slabs]
    const uint32_t* slab_begin;  // [P + 1] first slab of each partition
@@ -149,11 +160,17 @@ struct SeqDev {
    const uint2* miss_iv;          // [start, end) position intervals
    const uint64_t* miss_row_base; // [P] index of the partition's first row_off entry
    const uint64_t* miss_iv_base;  // [P]
+   // One 32-byte record per row with the row's first intervals inline, so that a kernel that needs the missing positions of a
+   // row issues ONE load instead of walking row_off -> intervals (dependent loads, two or three scattered sectors):
+   //   length <= 65,535 (miss_narrow): eight words start | end << 16, unused ones 0; otherwise four (start, end) word pairs.
+   //   A row with more intervals has every word 0xFFFFFFFF: its intervals are read from the CSR arrays above.
+   const uint4* miss_inline;         // [2 per row]
+   const uint64_t* miss_inline_base; // [P] index of the partition's first row
+   uint32_t miss_narrow, pad_inline;
    const uint32_t* miss_tile_bits;   // per partition [n_tiles][ceil(n_rows / 32)]: bit = the row misses some position of the tile
    const uint64_t* miss_tile_base;   // [P] word offset of the partition's block
    const uint32_t* part_rows;        // [P] sequence_count of the partition's store, 0 = the partition has no store of this sequence
-   const uint32_t* item_partition;   // [n_items] partition of items[i] (items are ordered heaviest first over the whole sequence)
-   uint32_t length, sigma, tile_positions, n_tiles, n_partitions, n_items, n_slabs;
+   uint32_t length, sigma, tile_positions, n_tiles, n_partitions, n_items, n_slabs, n_runs;
 };
 
 }  // namespace sb

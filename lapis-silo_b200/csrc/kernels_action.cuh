@@ -29,7 +29,6 @@ namespace sb {
 #define SB_K1_MIN_CTAS 4
 #endif
 constexpr int K1_THREADS = SB_K1_THREADS;   // 8 warps; up to 4 CTAs per SM (48-57 KB of shared memory each)
-constexpr int K1_UNROLL = SB_K1_UNROLL;     // 128-bit posting loads in flight per thread
 #ifdef SB_K1_TIMELINE
 // diagnostics build only: per-CTA time stamps {smid, start, filter ready, warp 0 out of units, after the barrier, end, units, weight}
 __device__ unsigned long long* g_k1_timeline = nullptr;
@@ -122,7 +121,7 @@ struct ActionPtrs {            // device arrays of one (query, sequence)
    uint32_t* partial;          // [P]
    uint32_t* full;             // [P]
    ActionHead* head;
-   uint32_t* selected;         // [n_items] indices into SeqDev::items of the partial partitions' work items, heaviest first
+   uint32_t* selected;         // [n_runs] indices into SeqDev::runs of the partial partitions' runs, heaviest first
 };
 struct ClassifyArgs {
    uint32_t seq_index, pad;    // into the database's SeqDev array
@@ -167,13 +166,13 @@ classify_partitions(const ClassifyBatch batch, const SeqDev* __restrict__ seqs, 
    }
 }
 
-// indices of the work items of the partial partitions, in the order of SeqDev::items (heaviest first; blocks may land out of order)
+// indices of the runs of the partial partitions, in the order of SeqDev::runs (heaviest first; blocks may land out of order)
 __global__ void __launch_bounds__(256)
-compact_items(const SeqDev s, const ActionPtrs a) {
+compact_runs(const SeqDev s, const ActionPtrs a) {
    __shared__ uint32_t warp_base[8];
    __shared__ uint32_t block_base;
    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, lane = laneId(), warp = threadIdx.x >> 5;
-   const bool take = i < s.n_items && a.pq[s.item_partition[i]].state == PART_PARTIAL;
+   const bool take = i < s.n_runs && a.pq[s.runs[i].partition].state == PART_PARTIAL;
    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, take);
    if (lane == 0) warp_base[warp] = __popc(mask);
    __syncthreads();
@@ -203,69 +202,90 @@ __global__ void k3_init_table(const uint32_t* __restrict__ full_tables, size_t t
 }
 
 // ---- K1: the container scan -----------------------------------------------------------------------------------------
-// Persistent CTAs (4 per SM) take the selected work items from a device counter, heaviest first. Shared memory:
-// [filter slab 32 KB][tile counts (tile_slots + 32 words)][mbarrier][unit counter][next item].
+// Persistent CTAs (4 per SM) take the selected RUNS of work items from a device counter, heaviest first; the items of a run
+// belong to one slab (ascending tiles), so the slab's 32 KB filter slice is copied once per run. Shared memory:
+// [filter slab 32 KB][tile counts (tile_slots + 32 words)][mbarrier][two unit counters][next item].
 // tile_counts[sym * T + pos_in_tile] accumulates the RAW |F AND B[pos][sym]|; the flipped / deleted-symbol arithmetic
-// (mutations.cpp:85-95, 122-133) is linear in it and is applied once per slot in the flush.
+// (mutations.cpp:85-95, 122-133) is linear in it and is applied once per slot in the flush, which also leaves the table
+// zeroed for the next item. Two CTA barriers per item: before its first increment (the previous flush is done) and before
+// its flush (all units are counted).
 struct K1Next { WorkItem item; const uint32_t* filter32; uint32_t valid, pad; };
 
-__global__ void __launch_bounds__(K1_THREADS, SB_K1_MIN_CTAS)
+// FLAGS (tuning, compiled side by side): 1 = a hit increments its slot with a predicated reduction (a miss costs no shared-memory
+// operation) instead of every posting incrementing either its slot or the lane's dummy slot; 2 = the directory entry of a
+// warp's next large container is fetched while the current one is counted.
+template <int UNROLL, int MIN_CTAS, int FLAGS>
+__global__ void __launch_bounds__(K1_THREADS, MIN_CTAS)
 k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int full_mode) {
+   constexpr int K1_UNROLL = UNROLL;
    extern __shared__ __align__(128) uint8_t k1_smem[];
    uint32_t* filter_s = reinterpret_cast<uint32_t*>(k1_smem);
    uint32_t* tile_counts = reinterpret_cast<uint32_t*>(k1_smem + K1_FILTER_BYTES);
    const uint32_t T = s.tile_positions, tile_slots = T * s.sigma;
    uint64_t* bar = reinterpret_cast<uint64_t*>(tile_counts + k1TableWords(tile_slots));
-   uint32_t* next_unit = reinterpret_cast<uint32_t*>(bar + 1);
-   K1Next* next_item = reinterpret_cast<K1Next*>(bar + 2);
+   uint32_t* unit_counters = reinterpret_cast<uint32_t*>(bar + 1);      // [2]: item i hands out its units through counter i & 1
+   K1Next* item_slots = reinterpret_cast<K1Next*>(bar + 2);      // [2]: the current item and the one thread 0 fetches meanwhile (read in place: no registers held)
+   constexpr uint32_t CHUNK4 = 32 * K1_UNROLL;    // 128-bit words per chunk
+   constexpr uint32_t N_WARPS = K1_THREADS / 32;
 
-   // the next item of this CTA: index from the device counter, the item by value, its partition's filter pointer
-   auto fetchNext = [&]() {
+   // thread 0 only: the item after the current one -- the next item of the run, or the first item of the next run from the
+   // device counter (index, run, item and filter pointer are dependent loads: fetched while the other warps stream)
+   uint32_t run_next = 0, run_end = 0;
+   const uint32_t* run_filter = nullptr;
+   auto fetchNext = [&](K1Next* into) {
       K1Next n{};
-      const uint32_t k = atomicAdd(&a.head->next_item, 1u);
-      if (k < a.head->n_selected) {
-         n.item = s.items[a.selected[k]];
-         n.filter32 = a.pq[n.item.partition].filter32;
-         n.valid = 1;
+      if (run_next == run_end) {
+         const uint32_t k = atomicAdd(&a.head->next_run, 1u);
+         if (k < a.head->n_selected) {
+            const RunRec run = s.runs[a.selected[k]];
+            run_next = run.first_item; run_end = run.first_item + run.n_items;
+            run_filter = a.pq[run.partition].filter32;
+         }
       }
-      *next_item = n;
+      if (run_next < run_end) { n.item = s.items[run_next++]; n.filter32 = run_filter; n.valid = 1; }
+      *into = n;
    };
    if (threadIdx.x == 0) {
       mbarInit(bar, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      fetchNext();
+      unit_counters[0] = N_WARPS;
+      fetchNext(item_slots);
    }
-   __syncthreads();
-   constexpr uint32_t CHUNK4 = 32 * K1_UNROLL;    // 128-bit words per chunk
-   constexpr uint32_t N_WARPS = K1_THREADS / 32;
+   for (uint32_t i = threadIdx.x; i < tile_slots + 32; i += K1_THREADS) tile_counts[i] = 0;
    const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
    const uint32_t dummy = tile_slots << POSTING_ROW_BITS;          // a posting of the slot that is never flushed
    const uint4 none = make_uint4(dummy, dummy, dummy, dummy);
-   uint32_t parity = 0;
+   uint32_t parity = 0, turn = 0;
    uint32_t cur_slab = 0xFFFFFFFFu;
-   for (;;) {
-      const K1Next cur = *next_item;
+   __syncthreads();
+   for (;; turn ^= 1u) {
+      const K1Next& cur = item_slots[turn];
       if (!cur.valid) break;
-      const WorkItem item = cur.item;
-      const bool new_slab = item.slab != cur_slab;        // consecutive items of one slab keep the filter slice
+      const WorkItem& item = cur.item;
+      const bool new_slab = item.slab != cur_slab;        // the items of a run keep the filter slice
       cur_slab = item.slab;
-      __syncthreads();                                    // everyone has read next_item; the previous flush is done
+      uint32_t* next_unit = unit_counters + turn;
+      __syncthreads();                                    // the previous flush (and its zeroing) is done; nobody reads the other item slot any more
       if (threadIdx.x == 0) {
          if (new_slab) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbarExpectTx(bar, K1_FILTER_BYTES);
             bulkLoad(filter_s, cur.filter32 + size_t(item.key0) * 2048u, K1_FILTER_BYTES, bar);
          }
-         *next_unit = N_WARPS;
+         unit_counters[turn ^ 1u] = N_WARPS;              // the next item's counter: nobody touches it before the next barrier
       }
-      for (uint32_t i = threadIdx.x; i < tile_slots + 32; i += K1_THREADS) tile_counts[i] = 0;
 
-      // flags of this thread's flush position, fetched now so that the flush does not wait for them
-      const uint32_t flush_pos = item.tile * T + threadIdx.x;
-      int flush_del = -1, flush_flip = -1;
-      if (threadIdx.x < T && flush_pos < s.length) {
-         flush_del = s.deleted[size_t(item.partition) * s.length + flush_pos];
-         flush_flip = s.flipped[size_t(item.partition) * s.length + flush_pos];
+      // flags of this thread's flush positions (one or two: a tile holds 256 or 512), fetched now so that the flush does not wait for them
+      constexpr uint32_t FLUSH_MAX = MAX_TILE_POSITIONS / K1_THREADS;
+      int flush_del[FLUSH_MAX], flush_flip[FLUSH_MAX];
+#pragma unroll
+      for (uint32_t f = 0; f < FLUSH_MAX; ++f) {
+         const uint32_t pl = threadIdx.x + f * K1_THREADS, pos = item.tile * T + pl;
+         flush_del[f] = flush_flip[f] = -1;
+         if (pl < T && pos < s.length) {
+            flush_del[f] = s.deleted[size_t(item.partition) * s.length + pos];
+            flush_flip[f] = s.flipped[size_t(item.partition) * s.length + pos];
+         }
       }
       // Work units of the item, handed out to the warps through a shared counter (a warp that is busy with a bitset
       // simply takes fewer): first the large containers -- a bitset as two halves of 4 KB, anything else whole --
@@ -289,14 +309,13 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
       };
       uint32_t unit = warp;
       loadChunk(unit, v);
-      __syncthreads();      // counts zeroed, unit counter initialised
       if (new_slab) { mbarWait(bar, parity); }
-      // thread 0 fetches the CTA's next item while the other warps stream: index, item and filter pointer are three
-      // dependent loads that would otherwise sit between two items
-      if (threadIdx.x == 0) fetchNext();
+      // thread 0 fetches the CTA's next item while the other warps stream
+      if (threadIdx.x == 0) fetchNext(item_slots + (turn ^ 1u));
 
       // Eight postings at a time: the eight filter words are fetched first (independent shared-memory loads), then the hits
       // are counted with unconditional shared-memory increments -- no data-dependent branch, one load round trip per eight postings.
+      const uint32_t counts_s = smemAddr(tile_counts);
       auto probe8 = [&](const uint4& p0, const uint4& p1) {
          const uint32_t p[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
          uint32_t w[8];
@@ -304,13 +323,26 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
          for (int t = 0; t < 8; ++t) w[t] = filter_s[(p[t] >> 5) & (SLAB_WORDS32 - 1)];
 #pragma unroll
          for (int t = 0; t < 8; ++t) {
-            const bool hit = (w[t] >> (p[t] & 31)) & 1u;
-            atomicAdd(&tile_counts[hit ? (p[t] >> POSTING_ROW_BITS) : tile_slots + lane], 1u);   // a miss increments the lane's dummy slot: no branch
+            const uint32_t hit = (w[t] >> (p[t] & 31)) & 1u;
+            if (FLAGS & 1) {
+               asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q red.shared.add.u32 [%1], 1; }" ::"r"(hit), "r"(counts_s + ((p[t] >> POSTING_ROW_BITS) << 2)) : "memory");
+            } else {
+               atomicAdd(&tile_counts[hit ? (p[t] >> POSTING_ROW_BITS) : tile_slots + lane], 1u);   // a miss increments the lane's dummy slot: no branch
+            }
          }
       };
+      LargeEntry w_ahead{};
+      if ((FLAGS & 2) && unit < n_large_units) w_ahead = s.large_entries[item.large_begin + (unit >> 1)];
       while (unit < n_units) {
          if (unit < n_large_units) {
-            const LargeEntry w = s.large_entries[item.large_begin + (unit >> 1)];
+            uint32_t grabbed = 0;
+            LargeEntry w = w_ahead;
+            if (FLAGS & 2) {      // take the next unit now: its directory entry travels while this container is counted
+               grabbed = grab();
+               if (grabbed < n_large_units) w_ahead = s.large_entries[item.large_begin + (grabbed >> 1)];
+            } else {
+               w = s.large_entries[item.large_begin + (unit >> 1)];
+            }
             const uint32_t half = unit & 1u;
             const uint4* src = s.large_pool + w.offset16;
             const uint32_t k_kind = w.kind(), k_local = w.keyLocal(), k_size = w.size;
@@ -349,7 +381,7 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
             }
             c2 = warpSum(c2);
             if (lane == 0 && c2 != 0) atomicAdd(&tile_counts[w.slot()], uint32_t(c2));
-            unit = grab();
+            unit = (FLAGS & 2) ? grabbed : grab();
             loadChunk(unit, v);
          } else {
             const uint32_t next = grab();
@@ -365,24 +397,28 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
       if (new_slab) parity ^= 1u;
       __syncthreads();
       // flush: thread = position of the tile; symbol rows of counts[sym][pos] get coalesced REDs
-      static_assert(TILE_POSITIONS <= K1_THREADS, "one flush position per thread");
-      if (threadIdx.x < T && flush_pos < s.length) {
-         const uint32_t pl = threadIdx.x;
+      static_assert(MAX_TILE_POSITIONS % K1_THREADS == 0, "whole flush positions per thread");
+#pragma unroll
+      for (uint32_t f = 0; f < FLUSH_MAX; ++f) {
+         const uint32_t pl = threadIdx.x + f * K1_THREADS, flush_pos = item.tile * T + pl;
+         if (pl >= T || flush_pos >= s.length) continue;
          int acc_deleted = 0;
          for (uint32_t sym0 = 0; sym0 < s.sigma; sym0 += 8) {      // eight counters in flight, then their REDs
             int raw[8];
 #pragma unroll
             for (uint32_t q = 0; q < 8; ++q) raw[q] = sym0 + q < s.sigma ? int(tile_counts[(sym0 + q) * T + pl]) : 0;
 #pragma unroll
+            for (uint32_t q = 0; q < 8; ++q) if (sym0 + q < s.sigma && raw[q] != 0) tile_counts[(sym0 + q) * T + pl] = 0;      // the next item starts from zero
+#pragma unroll
             for (uint32_t q = 0; q < 8; ++q) {
                const uint32_t sym = sym0 + q;
-               if (raw[q] == 0 || int(sym) == flush_del) continue;
-               const int add_slot = int(sym) == flush_flip ? -raw[q] : raw[q];
+               if (raw[q] == 0 || int(sym) == flush_del[f]) continue;
+               const int add_slot = int(sym) == flush_flip[f] ? -raw[q] : raw[q];
                atomicAdd(counts + size_t(sym) * s.length + flush_pos, uint32_t(add_slot));
                acc_deleted += full_mode ? -raw[q] : -add_slot;
             }
          }
-         if (flush_del >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(flush_del) * s.length + flush_pos, uint32_t(acc_deleted));
+         if (flush_del[f] >= 0 && acc_deleted != 0) atomicAdd(counts + size_t(flush_del[f]) * s.length + flush_pos, uint32_t(acc_deleted));
       }
    }
 }
@@ -429,31 +465,65 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
    const uint32_t* row_off = s.miss_row_off + s.miss_row_base[partition];
    const uint2* iv = s.miss_iv + s.miss_iv_base[partition];
    bool any_row = false;
-   for (uint32_t word = (row0 >> 5) + threadIdx.x; word < ((row1 + 31) >> 5); word += K2_THREADS) {
-      uint32_t bits = __ldg(q.filter32 + word);
-      if ((word + 1) * 32 > row1) bits &= ~0u >> (32 - (row1 & 31));      // row1 is the partition's end here: row blocks are multiples of 32 rows
-      while (bits) {
-         uint32_t b[4], e[4];
+   // A warp takes 1,024 rows (32 filter words) at a time and shares the FILTERED rows evenly over its lanes: lane l of round r
+   // owns the (128 r + 32 k + l)-th filtered row of the chunk, k < 4 (found with a search over the lanes' popcount prefix and
+   // __fns), so that every lane has four row_off pairs and then four interval loads in flight whatever the filter looks like.
+   const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
+   const uint32_t word_begin = row0 >> 5, word_end = (row1 + 31) >> 5;
+   int at_window_start = 0;      // intervals that begin at the window's first position (leading runs: nearly every row) are counted in a register
+   const uint4* records = s.miss_inline + s.miss_inline_base[partition] * 2;
+   auto apply = [&](uint32_t start, uint32_t end) {      // an empty slot is (0, 0): nothing happens
+      const uint32_t lo = max(start, w0), hi = min(end, w1);
+      if (lo < hi) {
+         if (lo == w0) ++at_window_start; else atomicAdd(&diff[lo - w0], 1);
+         if (hi < w1) atomicAdd(&diff[hi - w0], -1);      // diff[width] is never read
+      }
+   };
+   for (uint32_t base = word_begin + warp * 32; base < word_end; base += (K2_THREADS / 32) * 32) {
+      const uint32_t word = base + lane;
+      uint32_t bits = word < word_end ? __ldg(q.filter32 + word) : 0u;
+      if (word < word_end && (word + 1) * 32 > row1) bits &= ~0u >> (32 - (row1 & 31));      // row1 is the partition's end here: row blocks are multiples of 32 rows
+      const uint32_t mine = __popc(bits);
+      uint32_t incl = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
+      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31), excl = incl - mine;
+      if (total) any_row = true;
+      for (uint32_t r0 = 0; r0 < total; r0 += 128) {
+         uint4 rec[4][2];      // the rows' inline interval records: eight 128-bit loads in flight per lane, nothing depends on another load
+         uint32_t rows[4];
 #pragma unroll
          for (int k = 0; k < 4; ++k) {
-            b[k] = e[k] = 0;
-            if (bits) {
-               const uint32_t row = word * 32 + uint32_t(__ffs(int(bits))) - 1u;
-               bits &= bits - 1u;
-               b[k] = __ldg(row_off + row); e[k] = __ldg(row_off + row + 1);
+            const uint32_t n = r0 + k * 32 + lane, nn = min(n, total - 1);
+            uint32_t owner = 0;      // number of lanes whose inclusive prefix is <= nn = the lane that holds the nn-th filtered row
+#pragma unroll
+            for (uint32_t step = 16; step; step >>= 1) { const uint32_t v = __shfl_sync(0xFFFFFFFFu, incl, owner + step - 1); if (v <= nn) owner += step; }
+            const uint32_t owner_bits = __shfl_sync(0xFFFFFFFFu, bits, owner), owner_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
+            rows[k] = 0xFFFFFFFFu;
+            rec[k][0] = rec[k][1] = make_uint4(0, 0, 0, 0);
+            if (n < total) {
+               rows[k] = (base + owner) * 32 + __fns(owner_bits, 0, int(nn - owner_excl) + 1);
+               rec[k][0] = __ldg(records + size_t(rows[k]) * 2);
+               rec[k][1] = __ldg(records + size_t(rows[k]) * 2 + 1);
             }
          }
-         any_row = true;
 #pragma unroll
          for (int k = 0; k < 4; ++k) {
-            for (uint32_t j = b[k]; j < e[k]; ++j) {
-               const uint2 r = __ldg(iv + j);
-               const uint32_t lo = max(r.x, w0), hi = min(r.y, w1);
-               if (lo < hi) { atomicAdd(&diff[lo - w0], 1); atomicAdd(&diff[hi - w0], -1); }
+            const uint32_t w[8] = {rec[k][0].x, rec[k][0].y, rec[k][0].z, rec[k][0].w, rec[k][1].x, rec[k][1].y, rec[k][1].z, rec[k][1].w};
+            if (w[0] == 0xFFFFFFFFu && w[1] == 0xFFFFFFFFu) {      // more intervals than a record holds: the CSR arrays
+               for (uint32_t j = __ldg(row_off + rows[k]), e = __ldg(row_off + rows[k] + 1); j < e; ++j) { const uint2 r = __ldg(iv + j); apply(r.x, r.y); }
+            } else if (s.miss_narrow) {
+#pragma unroll
+               for (int t = 0; t < 8; ++t) apply(w[t] & 0xFFFFu, w[t] >> 16);
+            } else {
+#pragma unroll
+               for (int t = 0; t < 4; ++t) apply(w[2 * t], w[2 * t + 1]);
             }
          }
       }
    }
+   at_window_start = warpSum(at_window_start);
+   if (lane == 0 && at_window_start) atomicAdd(&diff[0], at_window_start);
    const bool first_block = found[1] == 0;
    if (!__syncthreads_or(any_row) && !first_block) return;
 
@@ -462,7 +532,6 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
    const uint32_t begin = min(threadIdx.x * per, width), end = min(begin + per, width);
    int sum = 0;
    for (uint32_t i = begin; i < end; ++i) sum += diff[i];
-   const uint32_t warp = threadIdx.x >> 5, lane = laneId();
    int incl = sum;
 #pragma unroll
    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }

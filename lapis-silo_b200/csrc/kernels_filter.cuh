@@ -151,30 +151,40 @@ leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict
    if (total) {
       const uint32_t* row_off = s.miss_row_off + s.miss_row_base[job.partition];
       const uint2* iv = s.miss_iv + s.miss_iv_base[job.partition];
-      // four candidates per lane at a time, their searches walked in lockstep: four independent chains of dependent loads
+      const uint4* records = s.miss_inline + s.miss_inline_base[job.partition] * 2;
+      // four candidates per lane at a time: their inline interval records are eight independent 128-bit loads; only a row with
+      // more intervals than a record holds (all words set) is searched in the CSR arrays
       for (uint32_t k0 = lane; k0 < total; k0 += 128) {
-         uint32_t row[4], lo[4], hi[4];
+         uint32_t row[4];
+         uint4 rec[4][2];
 #pragma unroll
          for (uint32_t q = 0; q < 4; ++q) {
-            lo[q] = hi[q] = 0; row[q] = 0;
-            if (k0 + q * 32 < total) { row[q] = cand_rows[warp][k0 + q * 32]; lo[q] = __ldg(row_off + row[q]); hi[q] = __ldg(row_off + row[q] + 1); }
+            row[q] = 0xFFFFFFFFu;
+            rec[q][0] = rec[q][1] = make_uint4(0, 0, 0, 0);
+            if (k0 + q * 32 < total) { row[q] = cand_rows[warp][k0 + q * 32]; rec[q][0] = __ldg(records + size_t(row[q]) * 2); rec[q][1] = __ldg(records + size_t(row[q]) * 2 + 1); }
          }
-         bool any = true;
-         while (any) {
-            any = false;
-            uint2 r[4];
-            uint32_t mid[4];
 #pragma unroll
-            for (uint32_t q = 0; q < 4; ++q) { mid[q] = (lo[q] + hi[q]) >> 1; if (lo[q] < hi[q]) r[q] = __ldg(iv + mid[q]); }
-#pragma unroll
-            for (uint32_t q = 0; q < 4; ++q) {
-               if (lo[q] < hi[q]) {
-                  if (job.value < r[q].x) hi[q] = mid[q];
-                  else if (job.value >= r[q].y) lo[q] = mid[q] + 1;
-                  else { atomicOr(&found_words[warp][(row[q] >> 5) & 31u], 1u << (row[q] & 31)); hi[q] = lo[q]; }
-                  any |= lo[q] < hi[q];
+         for (uint32_t q = 0; q < 4; ++q) {
+            if (row[q] == 0xFFFFFFFFu) continue;
+            const uint32_t w[8] = {rec[q][0].x, rec[q][0].y, rec[q][0].z, rec[q][0].w, rec[q][1].x, rec[q][1].y, rec[q][1].z, rec[q][1].w};
+            bool found = false;
+            if (w[0] == 0xFFFFFFFFu && w[1] == 0xFFFFFFFFu) {      // sorted, disjoint intervals: binary search
+               uint32_t lo = __ldg(row_off + row[q]), hi = __ldg(row_off + row[q] + 1);
+               while (lo < hi) {
+                  const uint32_t mid = (lo + hi) >> 1;
+                  const uint2 r = __ldg(iv + mid);
+                  if (job.value < r.x) hi = mid;
+                  else if (job.value >= r.y) lo = mid + 1;
+                  else { found = true; break; }
                }
+            } else if (s.miss_narrow) {
+#pragma unroll
+               for (int t = 0; t < 8; ++t) found |= job.value >= (w[t] & 0xFFFFu) && job.value < (w[t] >> 16);
+            } else {
+#pragma unroll
+               for (int t = 0; t < 4; ++t) found |= job.value >= w[2 * t] && job.value < w[2 * t + 1];
             }
+            if (found) atomicOr(&found_words[warp][(row[q] >> 5) & 31u], 1u << (row[q] & 31));
          }
       }
       __syncwarp();
@@ -282,6 +292,58 @@ __device__ __forceinline__ void stageContainer(uint32_t* staging, uint32_t kind,
    }
 }
 
+// What a leaf contributes to ONE container key, resolved before the program runs: the descriptor, location and directory loads
+// of a leaf are a chain of dependent loads, and a plan has many leaves -- one thread per leaf walks the chains of a whole
+// window of leaves side by side instead of the CTA walking them one leaf after the other.
+enum : uint32_t { RES_NONE = 0, RES_DIRECT = 1, RES_CONTAINER = 2, RES_POS = 3 };
+struct LeafRes {
+   const void* ptr;          // DIRECT: 64-bit words of this key as they lie (bitset container, dense scratch) | CONTAINER: payload
+   uint32_t mode;
+   uint32_t size;            // DIRECT: readable words (<= 1,024) | CONTAINER: cardinality / number of runs | POS: sequence index
+   uint32_t e_begin, e_end;  // POS: large entries (arrays, runs) of this key | CONTAINER: e_begin = kind
+   uint32_t post_begin, post_end;   // POS: postings of the slot in the slab (all of its keys)
+};
+static_assert(sizeof(LeafRes) == 32, "LeafRes must be 32 bytes");
+constexpr uint32_t EVAL_RES_WINDOW = 64;
+
+__device__ __forceinline__ LeafRes resolveLeaf(const EvalArgs& a, const LeafDesc& leaf, uint32_t chunk) {
+   LeafRes r{nullptr, RES_NONE, 0, 0, 0, 0, 0};
+   const uint32_t w_base = chunk * EVAL_WORDS;
+   if (leaf.kind == LEAF_DENSE) {
+      if (leaf.a > w_base) { r.ptr = a.scratch + leaf.off + w_base; r.mode = RES_DIRECT; r.size = min(EVAL_WORDS, leaf.a - w_base); }
+   } else if (leaf.kind == LEAF_POS) {
+      const uint32_t slab_local = chunk / SLAB_KEYS, key_local = chunk % SLAB_KEYS;
+      if (slab_local < leaf.b) {
+         const SeqDev& s = a.seqs[leaf.a];
+         const LeafLoc loc = a.locs[leaf.off + slab_local];
+         uint32_t e_begin = loc.large_end, e_end = loc.large_end;
+         for (uint32_t e = loc.large_begin; e < loc.large_end; ++e) {      // sorted by key inside the slot
+            const LargeEntry le = s.large_entries[e];
+            if (le.keyLocal() < key_local) continue;
+            if (le.keyLocal() > key_local) break;
+            if (le.kind() == KIND_BITSET) { r.ptr = s.large_pool + le.offset16; r.mode = RES_DIRECT; r.size = EVAL_WORDS; break; }
+            if (e_begin == loc.large_end) e_begin = e;
+            e_end = e + 1;
+         }
+         if (r.mode == RES_NONE && (e_begin < e_end || loc.post_begin < loc.post_end)) {
+            r.mode = RES_POS; r.size = leaf.a; r.e_begin = e_begin; r.e_end = e_end; r.post_begin = loc.post_begin; r.post_end = loc.post_end;
+         }
+      }
+   } else {
+      const RegContainer* containers = (leaf.kind == LEAF_REG ? a.reg_containers : a.up_containers) + leaf.a;
+      const uint16_t* pool = leaf.kind == LEAF_REG ? a.reg_pool : a.up_pool;
+      uint32_t lo = 0, hi = leaf.b;       // containers are sorted by key
+      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (containers[mid].key < chunk) lo = mid + 1; else hi = mid; }
+      if (lo < leaf.b && containers[lo].key == chunk) {
+         const RegContainer c = containers[lo];
+         r.ptr = pool + c.pay_off;
+         if (c.kind == KIND_BITSET) { r.mode = RES_DIRECT; r.size = EVAL_WORDS; }
+         else { r.mode = RES_CONTAINER; r.size = c.size; r.e_begin = c.kind; }
+      }
+   }
+   return r;
+}
+
 // grid: (ceil(max n_words_padded / 1024), n_plans). Thread t owns words t, t + 256, t + 512, t + 768 of the key.
 // Shared memory: [levels][1024] uint64 evaluation stack (GLOBAL_STACK: in global memory instead) + 8 KB staging bitset.
 template <bool GLOBAL_STACK>
@@ -289,6 +351,7 @@ __global__ void __launch_bounds__(EVAL_THREADS)
 eval_plans(const EvalArgs a) {
    extern __shared__ __align__(16) uint64_t eval_smem[];
    __shared__ int warp_sums[EVAL_PER_THREAD][EVAL_THREADS / 32];
+   __shared__ LeafRes res[EVAL_RES_WINDOW];
    const PlanDesc plan = a.plans[blockIdx.y];
    const uint32_t chunk = blockIdx.x, w_base = chunk * EVAL_WORDS, tid = threadIdx.x;
    if (w_base >= plan.n_words_padded) return;
@@ -306,6 +369,7 @@ eval_plans(const EvalArgs a) {
       const uint32_t* end = pc + plan.prog_len;
       const LeafDesc* leaves = a.leaves + plan.leaf_off;
       int sp = 0;      // entries on the stack: levels 0 .. sp-2 in `stk`, the top in `tos`
+      uint32_t res_begin = 0, res_end = 0;      // leaves [res_begin, res_end) of the plan are resolved in `res` (leaves are numbered in program order)
 #define SB_LEVEL(l, j) stk[size_t(l) * EVAL_WORDS + (j) * EVAL_THREADS + tid]
 #define SB_SPILL() do { if (sp > 0) { _Pragma("unroll") for (int j = 0; j < EVAL_PER_THREAD; ++j) SB_LEVEL(sp - 1, j) = tos[j]; } ++sp; } while (0)
       while (pc < end) {
@@ -330,53 +394,36 @@ eval_plans(const EvalArgs a) {
                break;
             }
             case P_LEAF: {
-               const LeafDesc leaf = leaves[__ldg(pc++)];
+               const uint32_t li = __ldg(pc++);
+               if (li >= res_end || li < res_begin) {      // uniform over the CTA: resolve the next window of leaves, one thread per leaf
+                  __syncthreads();
+                  if (tid < EVAL_RES_WINDOW && li + tid < plan.n_leaves) res[tid] = resolveLeaf(a, leaves[li + tid], chunk);
+                  res_begin = li; res_end = li + EVAL_RES_WINDOW;
+                  __syncthreads();
+               }
+               const LeafRes r = res[li - res_begin];
                SB_SPILL();
 #pragma unroll
                for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
-               if (leaf.kind == LEAF_DENSE) {
-                  const uint64_t* src = a.scratch + leaf.off;
+               if (r.mode == RES_DIRECT) {
+                  const uint64_t* direct = static_cast<const uint64_t*>(r.ptr);
 #pragma unroll
-                  for (int j = 0; j < EVAL_PER_THREAD; ++j) { const uint32_t w = w_base + j * EVAL_THREADS + tid; if (w < leaf.a) tos[j] = __ldg(src + w); }
-                  break;
-               }
-               const uint64_t* direct = nullptr;     // a bitset container of this key: read as it lies in the pool
-               bool staged = false;
-               if (leaf.kind == LEAF_POS) {
-                  const uint32_t slab_local = chunk / SLAB_KEYS, key_local = chunk % SLAB_KEYS;
-                  if (slab_local < leaf.b) {
-                     const SeqDev& s = a.seqs[leaf.a];
-                     const LeafLoc loc = a.locs[leaf.off + slab_local];
-                     for (uint32_t e = loc.large_begin; e < loc.large_end; ++e) {
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) if (uint32_t(j * EVAL_THREADS + tid) < r.size) tos[j] = __ldg(direct + j * EVAL_THREADS + tid);
+               } else if (r.mode != RES_NONE) {      // uniform over the CTA
+                  if (r.mode == RES_CONTAINER) {
+                     stageContainer(staging, r.e_begin, r.size, static_cast<const uint16_t*>(r.ptr));
+                  } else {
+                     const SeqDev& s = a.seqs[r.size];
+                     const uint32_t key_local = chunk % SLAB_KEYS;
+                     for (uint32_t e = r.e_begin; e < r.e_end; ++e) {
                         const LargeEntry le = s.large_entries[e];
-                        if (le.keyLocal() != key_local) continue;
-                        if (le.kind() == KIND_BITSET) { direct = reinterpret_cast<const uint64_t*>(s.large_pool + le.offset16); break; }
                         stageContainer(staging, le.kind(), le.size, reinterpret_cast<const uint16_t*>(s.large_pool + le.offset16));
-                        staged = true;
                      }
-                     if (!direct && loc.post_begin < loc.post_end) {
-                        for (uint32_t i = loc.post_begin + tid; i < loc.post_end; i += EVAL_THREADS) {
-                           const uint32_t p = __ldg(s.postings + i);
-                           if (((p >> 16) & (SLAB_KEYS - 1)) == key_local) stageBit(staging, p & 0xFFFFu);
-                        }
-                        staged = true;
+                     for (uint32_t i = r.post_begin + tid; i < r.post_end; i += EVAL_THREADS) {
+                        const uint32_t p = __ldg(s.postings + i);
+                        if (((p >> 16) & (SLAB_KEYS - 1)) == key_local) stageBit(staging, p & 0xFFFFu);
                      }
                   }
-               } else {
-                  const RegContainer* containers = (leaf.kind == LEAF_REG ? a.reg_containers : a.up_containers) + leaf.a;
-                  const uint16_t* pool = leaf.kind == LEAF_REG ? a.reg_pool : a.up_pool;
-                  uint32_t lo = 0, hi = leaf.b;       // containers are sorted by key
-                  while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (containers[mid].key < chunk) lo = mid + 1; else hi = mid; }
-                  if (lo < leaf.b && containers[lo].key == chunk) {
-                     const RegContainer c = containers[lo];
-                     if (c.kind == KIND_BITSET) direct = reinterpret_cast<const uint64_t*>(pool + c.pay_off);
-                     else { stageContainer(staging, c.kind, c.size, pool + c.pay_off); staged = true; }
-                  }
-               }
-               if (direct) {
-#pragma unroll
-                  for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = __ldg(direct + j * EVAL_THREADS + tid);
-               } else if (staged) {      // uniform over the CTA
                   __syncthreads();
 #pragma unroll
                   for (int j = 0; j < EVAL_PER_THREAD; ++j) { tos[j] = staging64[j * EVAL_THREADS + tid]; staging64[j * EVAL_THREADS + tid] = 0; }

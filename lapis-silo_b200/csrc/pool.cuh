@@ -126,30 +126,43 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<WorkItem> items;
    DeviceBuffer<SegRec> segs;
    DeviceBuffer<SlabRec> slabs;
-   DeviceBuffer<uint32_t> slab_begin, part_rows, item_partition;
+   DeviceBuffer<RunRec> runs;
+   DeviceBuffer<uint32_t> slab_begin, part_rows;
    DeviceBuffer<uint4> large_pool;
    std::vector<uint32_t> h_slab_begin;    // [P + 1]
    std::vector<uint32_t> h_part_rows;     // [P] sequence_count of the partition's store (0 = none)
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
-   DeviceBuffer<uint64_t> miss_row_base, miss_iv_base, miss_tile_base;
+   DeviceBuffer<uint64_t> miss_row_base, miss_iv_base, miss_tile_base, miss_inline_base;
+   DeviceBuffer<uint4> miss_inline;
    DeviceBuffer<uint32_t> miss_tile_bits;
    DeviceBuffer<uint32_t> full_tables;   // [P][sigma * length]
    DeviceBuffer<uint8_t> reference;      // [length] symbols of the reference sequence (row selection)
    DeviceBuffer<uint32_t> row_area;      // [4] counter + selected rows
    SeqDev dev{};
-   uint32_t n_items = 0, n_slabs = 0;
+   uint32_t n_items = 0, n_slabs = 0, n_runs = 0;
+   uint32_t k1_resident[8] = {1, 1, 1, 1, 1, 1, 1, 1};   // CTAs of k1_scan per SM, per compiled variant
    uint64_t n_postings = 0, n_large = 0;
 };
 
 struct RegisteredBitmap { uint32_t partition; uint32_t first_container, n_containers; uint32_t max_value; };   // containers in ascending key order
 
 struct Column { uint32_t partition; int dtype; uint32_t n; void* device = nullptr; };
+struct GroupColumn { uint32_t partition; uint32_t n; uint32_t* device = nullptr; };   // dictionary codes of a metadata column (group-by)
 
 inline uint64_t itemWeightCap() {   // bytes of postings + large payload per Mutations work item (SB_ITEM_CAP_KB: tuning)
    const char* e = getenv("SB_ITEM_CAP_KB");
    return (e && atoi(e) > 0 ? uint64_t(atoi(e)) : 128) * 1024;
+}
+
+// bytes of postings + large payload per RUN of work items (one slab, consecutive tiles): what a CTA of the scan takes at a time.
+// Large enough to pay for the 32 KB filter copy, small enough that every resident CTA gets several (SB_RUN_CAP_KB: tuning).
+inline uint64_t runWeightCap(uint64_t total_weight) {
+   const char* e = getenv("SB_RUN_CAP_KB");
+   if (e && atoi(e) > 0) return uint64_t(atoi(e)) * 1024;
+   (void)total_weight;
+   return 96 * 1024;      // measured at 40 M rows: 1 item per run, 96 KB and 256 KB runs take 0.177 / 0.177 / 0.195 ms (long runs cost balance at the end of the scan)
 }
 
 inline uint32_t arraySplit() {   // values per large-array entry (SB_ARRAY_SPLIT: tuning; a multiple of 8 keeps the pieces 16-byte aligned)
@@ -160,10 +173,15 @@ inline uint32_t arraySplit() {   // values per large-array entry (SB_ARRAY_SPLIT
 
 // Packs the ingested stores of one sequence into the tiled device layout.
 inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>& stores, uint32_t n_partitions, sb_pool_stats& stats) {
+   if (const char* e = getenv("SB_TILE_POSITIONS")) {      // tuning: 256 or 512 positions per tile (512 only while the tile's slots fit the posting's 14-bit field)
+      const uint32_t v = uint32_t(atoi(e));
+      if ((v == 256 || v == 512) && v * seq.sigma < 0x4000) seq.tile_positions = v;
+   }
    const uint32_t sigma = seq.sigma, tp = seq.tile_positions, L = seq.length;
    seq.n_tiles = (L + tp - 1) / tp;
    const uint32_t slots_per_tile = tp * sigma;
    SB_REQUIRE(slots_per_tile < 0x4000, "tile does not fit the 14-bit slot field (one value is the dummy slot)");
+   SB_REQUIRE(seq.n_tiles <= 0x4000, "sequence longer than 16,384 tiles of positions");
    // slabs: 4 container keys each
    std::vector<SlabRec> slabs;
    seq.h_slab_begin.assign(n_partitions + 1, 0);
@@ -244,7 +262,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
                   SB_REQUIRE(at / 2 < 0xFFFFFFFFull, "large pool beyond 64 GB");
                   large_pool.resize(at + size_t((n16 + 7) / 8) * 2, 0);
                   memcpy(large_pool.data() + at, src + first, size_t(n16) * 2);
-                  large_entries.push_back({uint32_t(at / 2), c.kind == KIND_ARRAY ? n16 : c.size, pk.slot2 | (uint32_t(c.kind) << 14) | (key_local << 16), 0});
+                  large_entries.push_back({uint32_t(at / 2), c.kind == KIND_ARRAY ? n16 : c.size, pk.slot2 | (uint32_t(c.kind) << 14) | (key_local << 16) | (tile << 18), slab_id});
                   large_bytes += 16 + uint64_t((n16 + 7) / 8) * 16;
                }
             }
@@ -263,15 +281,33 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
          SB_REQUIRE(postings.size() < 0xFFFFFFF0ull, "more than 2^32 postings in one sequence");
       }
    }
-   std::vector<uint32_t> item_partition(items.size());
-   {  // order: heaviest first over the whole sequence -- the scan's persistent CTAs take the selected items of a query in
-      // this order from a device counter (longest-processing-time hand-out)
+   // Items in (slab, tile) order, cut into RUNS: consecutive items of one slab up to a weight cap. A run is what a persistent
+   // CTA of the scan takes from the device counter (longest-processing-time hand-out: heaviest run first); inside a run the
+   // slab's filter slice stays in shared memory.
+   std::vector<RunRec> runs;
+   {
       std::vector<uint32_t> order(items.size());
       for (uint32_t k = 0; k < order.size(); ++k) order[k] = k;
-      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return item_weight[a] > item_weight[b]; });
+      std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return items[a].slab != items[b].slab ? items[a].slab < items[b].slab : items[a].tile < items[b].tile; });
       std::vector<WorkItem> sorted(items.size());
-      for (uint32_t k = 0; k < order.size(); ++k) { sorted[k] = items[order[k]]; item_partition[k] = sorted[k].partition; }
+      std::vector<uint64_t> sorted_weight(items.size());
+      uint64_t total_weight = 0;
+      for (uint32_t k = 0; k < order.size(); ++k) { sorted[k] = items[order[k]]; sorted_weight[k] = item_weight[order[k]]; total_weight += sorted_weight[k]; }
       items.swap(sorted);
+      item_weight.swap(sorted_weight);
+      const uint64_t run_cap = runWeightCap(total_weight);
+      std::vector<uint64_t> run_weight;
+      for (uint32_t k = 0; k < items.size(); ++k) {
+         const bool extend = !runs.empty() && items[runs.back().first_item].slab == items[k].slab && run_weight.back() + item_weight[k] <= run_cap && runs.back().n_items < 64;
+         if (extend) { runs.back().n_items++; run_weight.back() += item_weight[k]; }
+         else { runs.push_back({k, 1, items[k].partition, 0}); run_weight.push_back(item_weight[k]); }
+      }
+      std::vector<uint32_t> run_order(runs.size());
+      for (uint32_t k = 0; k < run_order.size(); ++k) run_order[k] = k;
+      std::stable_sort(run_order.begin(), run_order.end(), [&](uint32_t a, uint32_t b) { return run_weight[a] > run_weight[b]; });
+      std::vector<RunRec> sorted_runs(runs.size());
+      for (uint32_t k = 0; k < run_order.size(); ++k) { sorted_runs[k] = runs[run_order[k]]; sorted_runs[k].weight_kb = uint32_t(run_weight[run_order[k]] >> 10); }
+      runs.swap(sorted_runs);
    }
    while (postings.size() % 4) postings.push_back(filler);
    segs.back() = {uint32_t(postings.size()), uint32_t(large_entries.size())};
@@ -286,12 +322,25 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    std::vector<int8_t> deleted(size_t(n_partitions) * L, -1), flipped(size_t(n_partitions) * L, -1);
    std::vector<uint32_t> row_off;
    std::vector<uint2> iv;
-   std::vector<uint64_t> row_base(n_partitions, 0), iv_base(n_partitions, 0);
+   std::vector<uint64_t> row_base(n_partitions, 0), iv_base(n_partitions, 0), inline_base(n_partitions, 0);
+   std::vector<uint32_t> inline_words;      // 8 per row
+   const bool narrow = L <= 65535;
    for (uint32_t p = 0; p < n_partitions; ++p) {
       row_base[p] = row_off.size();
       iv_base[p] = iv.size();
+      inline_base[p] = inline_words.size() / 8;
       if (seq.store_of_partition[p] < 0) { row_off.push_back(0); continue; }
       HostStore& st = *stores[seq.store_of_partition[p]];
+      inline_words.resize(inline_words.size() + size_t(st.n_rows) * 8, 0u);
+      for (uint32_t row = 0; row < st.n_rows; ++row) {
+         uint32_t* rec = inline_words.data() + (inline_base[p] + row) * 8;
+         const uint32_t b = st.miss_row_off[row], e = st.miss_row_off[row + 1];
+         if (e - b > (narrow ? 8u : 4u)) { for (int k = 0; k < 8; ++k) rec[k] = 0xFFFFFFFFu; continue; }
+         for (uint32_t j = b; j < e; ++j) {
+            if (narrow) rec[j - b] = st.miss_iv[j].x | (st.miss_iv[j].y << 16);
+            else { rec[2 * (j - b)] = st.miss_iv[j].x; rec[2 * (j - b) + 1] = st.miss_iv[j].y; }
+         }
+      }
       memcpy(deleted.data() + size_t(p) * L, st.deleted.data(), L);
       memcpy(flipped.data() + size_t(p) * L, st.flipped.data(), L);
       row_off.insert(row_off.end(), st.miss_row_off.begin(), st.miss_row_off.end());
@@ -309,7 +358,8 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.postings.upload(postings);
    seq.large_entries.upload(large_entries);
    seq.items.upload(items);
-   seq.item_partition.upload(item_partition);
+   seq.n_runs = uint32_t(runs.size());
+   seq.runs.upload(runs);
    seq.h_part_rows.assign(n_partitions, 0);
    for (uint32_t p = 0; p < n_partitions; ++p) if (seq.store_of_partition[p] >= 0) seq.h_part_rows[p] = stores[seq.store_of_partition[p]]->n_rows;
    seq.part_rows.upload(seq.h_part_rows);
@@ -324,6 +374,11 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.miss_iv.upload(iv);
    seq.miss_row_base.upload(row_base);
    seq.miss_iv_base.upload(iv_base);
+   seq.miss_inline_base.upload(inline_base);
+   seq.miss_inline.alloc(inline_words.size() / 4);
+   if (!inline_words.empty()) SB_CUDA(cudaMemcpy(seq.miss_inline.ptr, inline_words.data(), inline_words.size() * 4, cudaMemcpyHostToDevice));
+   stats.missing_bytes += seq.miss_inline.bytes();
+   std::vector<uint32_t>().swap(inline_words);
    {  // coarse index of the missing-symbol intervals: per (partition, tile) the rows that miss some position of the tile.
       // BitmapSelection(position) then searches the intervals of those rows only (a few percent of the partition).
       std::vector<uint64_t> tile_base(n_partitions, 0);
@@ -346,7 +401,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
       SB_CUDA(cudaDeviceSynchronize());
       stats.missing_bytes += seq.miss_tile_bits.bytes();
    }
-   stats.directory_bytes += seq.large_entries.bytes() + seq.items.bytes() + seq.segs.bytes() + seq.slabs.bytes();
+   stats.directory_bytes += seq.large_entries.bytes() + seq.items.bytes() + seq.runs.bytes() + seq.segs.bytes() + seq.slabs.bytes();
    stats.payload_bytes += seq.postings.bytes() + seq.large_pool.bytes();
    stats.n_work_items += items.size();
    stats.n_chunks += large_entries.size();
@@ -355,7 +410,8 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    d.large_pool = seq.large_pool.ptr; d.deleted = seq.deleted.ptr; d.flipped = seq.flipped.ptr;
    d.miss_row_off = seq.miss_row_off.ptr; d.miss_iv = seq.miss_iv.ptr; d.miss_row_base = seq.miss_row_base.ptr; d.miss_iv_base = seq.miss_iv_base.ptr;
    d.miss_tile_bits = seq.miss_tile_bits.ptr; d.miss_tile_base = seq.miss_tile_base.ptr;
-   d.part_rows = seq.part_rows.ptr; d.item_partition = seq.item_partition.ptr;
+   d.miss_inline = seq.miss_inline.ptr; d.miss_inline_base = seq.miss_inline_base.ptr; d.miss_narrow = narrow ? 1u : 0u;
+   d.part_rows = seq.part_rows.ptr; d.runs = seq.runs.ptr; d.n_runs = seq.n_runs;
    d.length = L; d.sigma = sigma; d.tile_positions = tp; d.n_tiles = seq.n_tiles; d.n_partitions = n_partitions;
    d.n_items = seq.n_items; d.n_slabs = n_slabs;
 }

@@ -3,11 +3,14 @@
 // sequences of a query, api_filter.inc the filter evaluation (replaces Operator::evaluate), api_action.inc finalize + the
 // Mutations / Aggregated actions on evaluated filters, api_query.inc whole queries as one submission (and as CUDA graphs).
 #include <atomic>
+#include <shared_mutex>
 #include <dlfcn.h>
 #include <nccl.h>
 #include "common.cuh"
 #include "kernels_action.cuh"
+#include "kernels_scan2.cuh"
 #include "kernels_filter.cuh"
+#include "kernels_group.cuh"
 #include "pool.cuh"
 
 using namespace sb;
@@ -148,12 +151,11 @@ struct sb_db {
    bool overlap = true;
    uint32_t k1_ctas = getenv("SB_K1_CTAS") ? uint32_t(atoi(getenv("SB_K1_CTAS"))) : 0;   // tuning / tests: persistent CTAs of the container scan (0 = as many as are resident at once)
    uint32_t k1_pad_bytes = getenv("SB_K1_PAD_KB") ? uint32_t(atoi(getenv("SB_K1_PAD_KB"))) * 1024u : 0;   // experiments: extra dynamic shared memory per CTA (fewer CTAs per SM, more L1)
-   uint32_t k1_resident = 4;           // CTAs of k1_scan per SM (occupancy query at finalize)
-   // multi-rank: collectives of one communicator must be issued in one order on every rank (sb_comm_enter)
-   std::mutex ticket_mutex;
-   std::condition_variable ticket_cv;
-   uint64_t next_ticket = 0;
-   bool ticket_held = false;
+   uint32_t k1_variant = getenv("SB_K1_VARIANT") ? uint32_t(atoi(getenv("SB_K1_VARIANT"))) : 0;
+   // multi-rank: NCCL matches the collectives of a communicator by issue order, so a query that reduces (one ncclReduce per
+   // requested sequence) holds this lock from its first launch to its last: the reduces of two host threads never interleave.
+   // The ORDER of the queries must still be the same on every rank -- that is the caller's contract (include/silo_b200.h).
+   std::mutex collective_mutex;
 
    std::vector<std::unique_ptr<HostStore>> stores;
    std::vector<std::unique_ptr<Sequence>> seqs;
@@ -166,6 +168,8 @@ struct sb_db {
    DeviceBuffer<RegContainer> d_reg_containers;
    DeviceBuffer<uint16_t> d_reg_pool;
    std::vector<Column> columns;
+   std::vector<GroupColumn> group_columns;      // may grow after finalize (a column is coded when a query first groups by it)
+   std::shared_mutex group_mutex;
 
    sb_pool_stats stats{};
 
@@ -173,12 +177,18 @@ struct sb_db {
       cudaSetDevice(device);
       if (comm) { sb::NcclApi::get().commDestroy(comm); comm = nullptr; }
       for (auto& c : columns) if (c.device) cudaFree(c.device);
+      for (auto& c : group_columns) if (c.device) cudaFree(c.device);
       if (ev_timer_begin) { cudaEventDestroy(ev_timer_begin); cudaEventDestroy(ev_timer_end); }
       lanes.clear();
    }
 };
 
 namespace sb {
+inline std::unique_lock<std::mutex> collectiveLock(sb_db* db) {      // held only while a communicator is active
+   std::unique_lock<std::mutex> lock(db->collective_mutex, std::defer_lock);
+   if (db->comm) lock.lock();
+   return lock;
+}
 inline void useDevice(const sb_db* db) { SB_CUDA(cudaSetDevice(db->device)); }
 // the lane of the calling thread (threads are numbered in the order in which they first call in)
 inline sb_lane* laneOf(sb_db* db) {
@@ -397,6 +407,7 @@ int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, 
 #include "api_filter.inc"
 #include "api_action.inc"
 #include "api_query.inc"
+#include "api_group.inc"
 
 // ---- row selection without any allocation ------------------------------------------------------------------------------
 // For callers that must not reach cudaMalloc (graph capture around them, tight serving loops, harnesses that forbid it):

@@ -169,6 +169,7 @@ inline std::unique_ptr<Database> buildDatabase(
    for (const auto& [name, seq] : aa_refs) db->aa_reference[name] = toSymbols(aminoAcidAlphabet(), seq, "reference " + name);
    for (const auto& m : db->config.metadata) {
       if (m.type == ColumnType::INDEXED_STRING || m.type == ColumnType::INDEXED_PANGOLINEAGE) db->dictionaries[m.name] = std::make_unique<Dictionary<std::string>>();
+      if (m.type == ColumnType::INDEXED_PANGOLINEAGE) db->aliased_dictionaries[m.name] = std::make_unique<Dictionary<std::string>>();
    }
    auto groups = partitionRecords(records, db->config.partition_by);
    const std::string& pk = db->config.primary_key;
@@ -203,7 +204,7 @@ inline std::unique_ptr<Database> buildDatabase(
             }
             case ColumnType::INDEXED_PANGOLINEAGE: {
                auto& c = part->columns.pango_lineage_columns[m.name];
-               c.alias = &db->alias; c.lookup_unaliased = db->dictionaries[m.name].get();
+               c.alias = &db->alias; c.lookup_unaliased = db->dictionaries[m.name].get(); c.lookup_aliased = db->aliased_dictionaries[m.name].get();
                for (size_t r : rows) c.insert(value(r).value_or(""));
                break;
             }

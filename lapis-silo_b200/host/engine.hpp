@@ -19,6 +19,7 @@
 #include <unordered_map>
 
 #include "../../include/silo_b200.h"
+#include "group_by.hpp"
 #include "optree_json.hpp"
 #include "query.hpp"
 
@@ -364,6 +365,45 @@ class DeviceDatabase {
       return count;
    }
 
+   // ---- Aggregated with groupByFields (aggregated.cpp:91-149) ------------------------------------------------------------
+   // The group-by columns are coded and uploaded when a query first names them (one pass over the column on the host).
+   const GroupDictionary& groupDictionary(const ColumnMetadata& meta) const {
+      std::lock_guard<std::mutex> lock(group_mutex_);
+      auto it = group_dictionaries_.find(meta.name);
+      if (it != group_dictionaries_.end()) return *it->second;
+      auto d = std::make_unique<GroupDictionary>(buildGroupDictionary(db, owned, meta));
+      for (uint32_t local = 0; local < owned.size(); ++local) {
+         uint32_t id = 0;
+         check(sb_group_column_add(handle, local, d->codes[local].data(), static_cast<uint32_t>(d->codes[local].size()), &id));
+         d->column_ids.push_back(id);
+      }
+      std::vector<std::vector<uint32_t>>().swap(d->codes);
+      return *(group_dictionaries_[meta.name] = std::move(d));
+   }
+   QueryResult executeGrouped(const Query& query) const {
+      const Action& action = query.action;
+      const std::vector<ColumnMetadata> fields = parseGroupByFields(db.config, action.group_by_fields);   // validateOrderByFields starts with it (aggregated.cpp:71-73)
+      return action.executeAndOrder([&]() -> QueryResult {
+         if (owned.empty()) return {};
+         CompiledFilter cf;
+         compileFilter(*query.filter, cf);
+         EvaluatedFilters filters = evaluatePlans(cf.plans);
+         std::vector<const GroupDictionary*> dictionaries;
+         std::vector<uint32_t> cardinalities, ids(owned.size() * fields.size());
+         for (const auto& meta : fields) { dictionaries.push_back(&groupDictionary(meta)); cardinalities.push_back(dictionaries.back()->cardinality); }
+         for (size_t local = 0; local < owned.size(); ++local) for (size_t c = 0; c < fields.size(); ++c) ids[local * fields.size() + c] = dictionaries[c]->column_ids[local];
+         std::vector<sb_group_row> rows(4096);
+         size_t n = 0;
+         for (;;) {
+            check(sb_aggregated_grouped(handle, static_cast<uint32_t>(filters.results.size()), filters.partitions.data(), filters.results.data(), static_cast<uint32_t>(fields.size()),
+                                        ids.data(), cardinalities.data(), rows.data(), rows.size(), &n));
+            if (n <= rows.size()) break;
+            rows.resize(n);
+         }
+         return groupedResult(dictionaries, rows.data(), n);
+      });
+   }
+
    // ---- one query = one submission (include/silo_b200.h: sb_query_mutations / sb_query_prepare) -----------------------
    // compile + lower per partition (query_engine.cpp:41-46 does it one partition after the other; the partitions are
    // independent, so with more than a few of them the worker pool shares the work)
@@ -481,7 +521,7 @@ class DeviceDatabase {
 
    QueryResult executeQuery(const std::string& query_string) const {
       Query query = parseQuery(query_string);
-      if (query.action.type == ActionType::AGGREGATED && !query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+      if (query.action.type == ActionType::AGGREGATED && !query.action.group_by_fields.empty()) return executeGrouped(query);
       std::vector<std::string> names;
       if (query.action.type != ActionType::AGGREGATED) names = mutationSequenceNames(query.action);
       CompiledFilter cf;
@@ -548,7 +588,7 @@ class DeviceDatabase {
       Query query = parseQuery(query_string);
       const Action& action = query.action;
       trace.lap("parse");
-      if (action.type == ActionType::AGGREGATED && !action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+      if (action.type == ActionType::AGGREGATED && !action.group_by_fields.empty()) return dumpJson(executeGrouped(query));
       action.validateOrderByFields();
       std::vector<std::string> names;
       if (action.type != ActionType::AGGREGATED) names = mutationSequenceNames(action);
@@ -604,6 +644,8 @@ class DeviceDatabase {
    }
    mutable std::mutex pool_mutex_;
    mutable std::unique_ptr<WorkerPool> pool_;
+   mutable std::mutex group_mutex_;
+   mutable std::map<std::string, std::unique_ptr<GroupDictionary>> group_dictionaries_;
 
    struct StoreRange { const Bitmap* begin; const Bitmap* end; uint32_t store_id; uint32_t sigma; };
    std::vector<StoreRange> store_ranges;

@@ -69,16 +69,17 @@ struct Action {
    ActionType type = ActionType::AGGREGATED;
    std::vector<std::string> sequence_names;  // Mutations
    double min_proportion = 0;                // Mutations
-   std::vector<std::string> group_by_fields; // Aggregated (non-empty: outside the hot path)
+   std::vector<std::string> group_by_fields; // Aggregated
    std::vector<OrderByField> order_by_fields;
    std::optional<uint32_t> limit, offset;
 
    int alphabetId() const { return type == ActionType::AA_MUTATIONS ? 1 : 0; }
 
-   void validateOrderByFields() const {  // mutations.cpp:167-183, aggregated.cpp:71-88 (no group-by: only "count")
+   void validateOrderByFields() const {  // mutations.cpp:167-183, aggregated.cpp:71-88 (the group-by fields exist: parseGroupByFields ran before)
       for (const auto& f : order_by_fields) {
          if (type == ActionType::AGGREGATED) {
-            CHECK_SILO_QUERY(f.name == "count", "The orderByField '" + f.name + "' cannot be ordered by, as it does not appear in the groupByFields.")
+            CHECK_SILO_QUERY(f.name == "count" || std::find(group_by_fields.begin(), group_by_fields.end(), f.name) != group_by_fields.end(),
+                             "The orderByField '" + f.name + "' cannot be ordered by, as it does not appear in the groupByFields.")
          } else {
             CHECK_SILO_QUERY(f.name == "mutation" || f.name == "proportion" || f.name == "count",
                              "OrderByField " + f.name + " is not contained in the result of this operation.")

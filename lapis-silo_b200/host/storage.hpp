@@ -128,11 +128,36 @@ struct PangoLineageAliasLookup {
       if (dot == std::string::npos) return it->second[0];
       return it->second[0] + '.' + lineage.substr(dot + 1);
    }
+   // storage/pango_lineage_alias.cpp:49-79: the longest prefix of at least three elements that some alias stands for is
+   // replaced by that alias (the reference walks its unordered_map; with several aliases of one value the choice is its
+   // iteration order, here the smallest alias name)
+   std::string alias(const std::string& lineage) const {
+      std::vector<std::string> elements;
+      for (size_t at = 0;;) {
+         const size_t dot = lineage.find('.', at);
+         elements.push_back(lineage.substr(at, dot == std::string::npos ? std::string::npos : dot - at));
+         if (dot == std::string::npos) break;
+         at = dot + 1;
+      }
+      for (size_t i = elements.size(); i > 3; --i) {
+         std::string search;
+         for (size_t k = 0; k + 1 < i; ++k) search += (k ? "." : "") + elements[k];
+         const std::string* best = nullptr;
+         for (const auto& [name, values] : alias_key) if (values.size() == 1 && values[0] == search && (!best || name < *best)) best = &name;
+         if (best) {
+            std::string value = *best;
+            for (size_t k = i - 1; k < elements.size(); ++k) value += "." + elements[k];
+            return value;
+         }
+      }
+      return lineage;
+   }
 };
 
 struct PangoLineageColumnPartition {
    const PangoLineageAliasLookup* alias = nullptr;
    Dictionary<std::string>* lookup_unaliased = nullptr;
+   Dictionary<std::string>* lookup_aliased = nullptr;   // filled side by side with lookup_unaliased (pango_lineage_column.cpp:21-33); optional
    std::vector<uint32_t> value_ids;
    std::unordered_map<uint32_t, Bitmap> indexed_values;
    std::unordered_map<uint32_t, Bitmap> indexed_sublineage_values;
@@ -150,12 +175,22 @@ struct PangoLineageColumnPartition {
    void insert(const std::string& raw) {  // pango_lineage_column.cpp:21-55 (null -> "")
       const std::string resolved = alias->unalias(raw);
       const auto parents = parentLineages(resolved);
-      for (const auto& p : parents) (void)lookup_unaliased->getOrCreateId(p);
+      for (const auto& p : parents) {
+         (void)lookup_unaliased->getOrCreateId(p);
+         if (lookup_aliased) (void)lookup_aliased->getOrCreateId(alias->alias(p));
+      }
       const uint32_t id = lookup_unaliased->getOrCreateId(resolved);
+      if (lookup_aliased) (void)lookup_aliased->getOrCreateId(alias->alias(resolved));
       const uint32_t row = static_cast<uint32_t>(value_ids.size());
       value_ids.push_back(id);
       indexed_values[id].add(row);
       for (const auto& p : parents) indexed_sublineage_values[lookup_unaliased->getOrCreateId(p)].add(row);
+   }
+   // pango_lineage_column.cpp:82-84: the value Aggregated / Details print for an id -- the id is one of lookup_unaliased and is
+   // looked up in lookup_aliased, as the reference does
+   std::string lookupAliasedValue(uint32_t id) const {
+      if (lookup_aliased) return id < lookup_aliased->values.size() ? lookup_aliased->values[id] : std::string();
+      return alias->alias(lookup_unaliased->values.at(id));
    }
    const Bitmap* filter(const std::string& value, bool include_sublineages) const {  // :57-77
       auto id = lookup_unaliased->getId(alias->unalias(value));
@@ -210,6 +245,7 @@ struct Database {
    std::vector<std::unique_ptr<DatabasePartition>> partitions;
    PangoLineageAliasLookup alias;
    std::map<std::string, std::unique_ptr<Dictionary<std::string>>> dictionaries;  // per indexed / lineage column
+   std::map<std::string, std::unique_ptr<Dictionary<std::string>>> aliased_dictionaries;  // per lineage column: lookup_aliased
 
    const std::map<std::string, std::vector<Symbol>>& getReferences(int alphabet_id) const {
       return alphabet_id == 0 ? nuc_reference : aa_reference;

@@ -361,15 +361,101 @@ inline QueryResult aggregateWithoutGrouping(const std::vector<OperatorResult>& f
    return QueryResult{{entry}};
 }
 
+// ---- Aggregated with groupByFields: aggregated.cpp:24-40 (parseGroupByFields), :91-149 (execute), tuple.cpp:29-155 ----
+// A tuple is the byte string of the row's group-by values exactly as assignTupleField lays them out: Date / int32 / double
+// raw, the dictionary id for indexed and lineage columns. The reference's String<N> (inline prefix + dictionary id of the
+// rest) is one-to-one with the text, which stands for it here behind a length.
+struct TupleLayout {
+   std::vector<ColumnMetadata> fields;
+};
+inline std::vector<ColumnMetadata> groupByMetadata(const Database& db, const std::vector<std::string>& group_by_fields) {   // aggregated.cpp:24-40
+   std::vector<ColumnMetadata> out;
+   for (const auto& field : group_by_fields) {
+      bool found = false;
+      for (const auto& m : db.config.metadata) if (m.name == field) { out.push_back(m); found = true; break; }
+      CHECK_SILO_QUERY(found, "Metadata field '" + field + "' to group by not found")
+   }
+   return out;
+}
+inline void appendTupleField(std::string& tuple, const ColumnMetadata& m, const ColumnPartitionGroup& columns, uint32_t row) {   // tuple.cpp:29-76
+   auto raw = [&](const void* p, size_t n) { tuple.append(static_cast<const char*>(p), n); };
+   auto text = [&](const std::string& v) { const uint32_t n = static_cast<uint32_t>(v.size()); raw(&n, 4); tuple += v; };
+   switch (m.type) {
+      case ColumnType::DATE: { const uint32_t v = columns.date_columns.at(m.name).values[row]; raw(&v, 4); break; }
+      case ColumnType::INT: { const int32_t v = columns.int_columns.at(m.name).values[row]; raw(&v, 4); break; }
+      case ColumnType::FLOAT: { const double v = columns.float_columns.at(m.name).values[row]; raw(&v, 8); break; }
+      case ColumnType::STRING: text(columns.string_columns.at(m.name).values[row]); break;
+      case ColumnType::INDEXED_STRING: { const uint32_t v = columns.indexed_string_columns.at(m.name).value_ids[row]; raw(&v, 4); break; }
+      case ColumnType::INDEXED_PANGOLINEAGE: { const uint32_t v = columns.pango_lineage_columns.at(m.name).value_ids[row]; raw(&v, 4); break; }
+      case ColumnType::NUC_INSERTION: text(columns.nuc_insertion_columns.at(m.name).values[row]); break;
+      case ColumnType::AA_INSERTION: text(columns.aa_insertion_columns.at(m.name).values[row]); break;
+   }
+}
+inline std::map<std::string, FieldValue> tupleFields(const std::string& tuple, const std::vector<ColumnMetadata>& fields, const ColumnPartitionGroup& columns) {   // tuple.cpp:78-155
+   std::map<std::string, FieldValue> out;
+   size_t at = 0;
+   auto take = [&](void* p, size_t n) { memcpy(p, tuple.data() + at, n); at += n; };
+   auto text = [&]() { uint32_t n; take(&n, 4); std::string v = tuple.substr(at, n); at += n; return v; };
+   auto orNull = [](std::string v) -> FieldValue { if (v.empty()) return std::nullopt; return v; };
+   for (const auto& m : fields) {
+      switch (m.type) {
+         case ColumnType::DATE: {      // common/date.cpp:66-80
+            uint32_t v; take(&v, 4);
+            if (v == 0) { out[m.name] = std::nullopt; break; }
+            char buffer[32];
+            snprintf(buffer, sizeof buffer, "%04u-%02u-%02u", v >> 16, (v >> 12) & 0xF, v & 0xFFF);
+            out[m.name] = std::string(buffer);
+            break;
+         }
+         case ColumnType::INT: { int32_t v; take(&v, 4); if (v == INT32_MIN) out[m.name] = std::nullopt; else out[m.name] = v; break; }
+         case ColumnType::FLOAT: { double v; take(&v, 8); if (std::isnan(v)) out[m.name] = std::nullopt; else out[m.name] = v; break; }
+         case ColumnType::STRING: case ColumnType::NUC_INSERTION: case ColumnType::AA_INSERTION: out[m.name] = orNull(text()); break;
+         case ColumnType::INDEXED_STRING: { uint32_t v; take(&v, 4); out[m.name] = orNull(columns.indexed_string_columns.at(m.name).lookup->values.at(v)); break; }
+         case ColumnType::INDEXED_PANGOLINEAGE: { uint32_t v; take(&v, 4); out[m.name] = orNull(columns.pango_lineage_columns.at(m.name).lookupAliasedValue(v)); break; }
+      }
+   }
+   return out;
+}
+inline QueryResult aggregateGrouped(const Database& db, const std::vector<std::string>& group_by_fields, const std::vector<OperatorResult>& filters) {   // aggregated.cpp:91-149
+   const std::vector<ColumnMetadata> fields = groupByMetadata(db, group_by_fields);
+   std::vector<std::unordered_map<std::string, uint32_t>> tuple_maps(db.partitions.size());
+   for (size_t p = 0; p < db.partitions.size(); ++p) {      // :111-137, one map per partition
+      const ColumnPartitionGroup& columns = db.partitions[p]->columns;
+      std::string tuple;
+      filters[p].get().forEach([&](uint32_t row) {
+         tuple.clear();
+         for (const auto& m : fields) appendTupleField(tuple, m, columns, row);
+         ++tuple_maps[p][tuple];
+      });
+   }
+   std::unordered_map<std::string, uint32_t> final_map;      // :138-148
+   const ColumnPartitionGroup* any_columns = nullptr;
+   for (size_t p = 0; p < db.partitions.size(); ++p) {
+      for (const auto& [tuple, count] : tuple_maps[p]) final_map[tuple] += count;
+      if (!tuple_maps[p].empty()) any_columns = &db.partitions[p]->columns;
+   }
+   QueryResult result;      // generateResult, :46-56
+   for (const auto& [tuple, count] : final_map) {
+      QueryResultEntry entry;
+      entry.fields = tupleFields(tuple, fields, *any_columns);
+      entry.fields["count"] = static_cast<int32_t>(count);
+      result.query_result.push_back(std::move(entry));
+   }
+   // the reference hands the rows out in the order of its hash map; a fixed order (every field, then the count) keeps runs comparable
+   std::sort(result.query_result.begin(), result.query_result.end(), [](const QueryResultEntry& a, const QueryResultEntry& b) { return a.fields < b.fields; });
+   return result;
+}
+
 // query_engine.cpp:30-68
 inline QueryResult executeQuery(const Database& db, const std::string& query_string, const Options& options,
                                 std::map<std::string, std::vector<uint32_t>>* tables = nullptr) {
    Query query = parseQuery(query_string);
    std::vector<operators::OperatorPtr> trees;
    std::vector<OperatorResult> filters = evaluateFilters(db, *query.filter, &trees, options.partitions);
+   if (query.action.type == ActionType::AGGREGATED) (void)groupByMetadata(db, query.action.group_by_fields);   // validateOrderByFields starts with it (aggregated.cpp:71-73)
    return query.action.executeAndOrder([&]() -> QueryResult {
       if (query.action.type == ActionType::AGGREGATED) {
-         if (!query.action.group_by_fields.empty()) throw QueryCompilationException("Aggregated with groupByFields is outside the hot path (SURVEY 8f)");
+         if (!query.action.group_by_fields.empty()) return aggregateGrouped(db, query.action.group_by_fields, filters);
          return aggregateWithoutGrouping(filters);
       }
       return executeMutations(db, query.action, filters, options, tables);

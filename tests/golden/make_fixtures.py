@@ -4,7 +4,7 @@ Copies DATA, never source code:
   * exampleDataset/            the reference's 100-sequence test dataset inputs (testBaseData/exampleDataset)
   * exampleDataset1000Sequences/  BASELINE config C1 inputs
   * queries/*.json             the end-to-end golden vectors of endToEndTests/test/queries that are on the
-                               hot path (Aggregated without groupByFields, Mutations, AminoAcidMutations)
+                               hot path (Aggregated with and without groupByFields, Mutations, AminoAcidMutations)
   * invalidQueries/*.json      the invalid-query fixtures (expected HTTP 400 message)
   * queries_out_of_scope.txt   names of the fixtures that were skipped and why
 """
@@ -42,7 +42,7 @@ def main():
         for path in sorted((REF / "endToEndTests" / "test" / sub).glob("*.json")):
             case = json.loads(path.read_text())
             action = case["query"].get("action", {}) if isinstance(case.get("query"), dict) else {}
-            hot = action.get("type") in HOT_ACTIONS and not action.get("groupByFields")
+            hot = action.get("type") in HOT_ACTIONS
             if sub == "queries" and not hot:
                 skipped.append(f"{path.name}\t{action.get('type')}{' +groupByFields' if action.get('groupByFields') else ''}")
                 continue

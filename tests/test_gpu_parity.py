@@ -84,7 +84,7 @@ def test_invalid_query_fixture(libs, example_engine, path):
     action = case["query"].get("action", {})
     with pytest.raises(pysilo.SiloError) as err:
         example_engine.execute(case["query"])
-    if action.get("type") in ("Details", "Fasta", "FastaAligned", "Insertions", "AminoAcidInsertions") or action.get("groupByFields"):
+    if action.get("type") in ("Details", "Fasta", "FastaAligned", "Insertions", "AminoAcidInsertions"):
         pytest.skip("action outside the hot path")
     assert err.value.kind == "parse" and err.value.message == case["expectedError"]["message"]
 
@@ -233,11 +233,15 @@ def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
     assert failures == []
 
 
-@pytest.mark.parametrize("env", [{"SB_K1_CTAS": "1"}, {"SB_K1_CTAS": "3"}, {"SB_K1_CTAS": "7"}, {"SB_K1_CTAS": "4000"}, {"SB_ITEM_CAP_KB": "4"}],
+@pytest.mark.parametrize("env", [{"SB_K1_CTAS": "1"}, {"SB_K1_CTAS": "3"}, {"SB_K1_CTAS": "7"}, {"SB_K1_CTAS": "4000"}, {"SB_ITEM_CAP_KB": "4"},
+                                 {"SB_RUN_CAP_KB": "1"}, {"SB_RUN_CAP_KB": "4096"}, {"SB_TILE_POSITIONS": "512"},
+                                 {"SB_K1_VARIANT": "1"}, {"SB_K1_VARIANT": "2"}, {"SB_K1_VARIANT": "4", "SB_K1_CTAS": "5"}, {"SB_K1_VARIANT": "6", "SB_ITEM_CAP_KB": "4"},
+                                 {"SB_K1_VARIANT": "7", "SB_TILE_POSITIONS": "512"}],
                          ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
 def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch):
-    """the container scan with odd numbers of persistent CTAs (one CTA takes every item, more CTAs than items) and with tiny
-    work items (many items per segment), against the oracle"""
+    """the container scan with odd numbers of persistent CTAs (one CTA takes every item, more CTAs than items), with tiny work
+    items (many items per segment), one item or a whole slab per run, 512-position tiles, and in its other compiled shapes
+    (k1_scan without predicated increments, k1_pipe at several depths), against the oracle"""
     pysilo, oracle = libs
     for k, v in env.items():
         monkeypatch.setenv(k, v)      # read when the device database is created
