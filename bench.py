@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--rows", type=int, default=int(os.environ.get("SILO_BENCH_ROWS", 40_000_000)))
     ap.add_argument("--seed", type=lambda s: int(s, 0), default=0x51100005)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--full-pass", action="store_true", help="--impl reference: measure the sample's share of the query by one full pass of the CPU restatement (minutes at 40 M rows)")
     ap.add_argument("--weak", action="store_true", help="N > 1: every rank holds its own shard of --rows sequences (replicated shards) instead of a share of one database")
     ap.add_argument("--lineage", action="store_true", help="also measure the C5 lineage and True queries (full / partial / empty partitions)")
     ap.add_argument("--in-flight", type=int, default=8, help="queries in flight of the extra throughput measurement (N = 1 only; 0 = skip)")
@@ -137,12 +138,14 @@ def cpu_calibrate(db, query, budget_s=3.0):
     return full, sample, t, cores, times
 
 
-def cpu_baseline_line(db, query, rows, budget_s=20.0):
-    """The in-line CPU baseline of the default run: a BOUNDED sample (about budget_s of CPU work) of the same query. The
-    reference's Mutations loop costs O(|F_p| * L) per partition (mutations.cpp:74-83: one contains() per filtered row and
-    position), so the sample -- partitions in a fixed pseudo-random order until the budget is spent -- is scaled to the whole
-    query by FILTERED rows, not by rows (a partition the filter does not select costs nothing). `--impl reference` measures
-    the full pass and prints per-partition times next to the filtered rows, so the estimator can be checked."""
+def cpu_baseline_line(db, query, rows):
+    """The in-line CPU baseline of the default run: a BOUNDED sample (10-30 s of CPU work) of the same query. The reference's
+    Mutations loop (mutations.cpp:66-136) walks the positions in chunks of 300 over its thread pool and spends, per position
+    and partition, O(|F_p|) contains() calls: its cost is (filtered rows) x (positions) -- measured at 1 M rows: 136-165 us per
+    filtered row in every partition, and 20.7 s estimated from a third of the positions against 20.3-23.1 s measured. The sample
+    cuts both ways -- about 30 % of the filtered rows (partitions in a fixed pseudo-random order) on the first 600 positions per
+    host thread -- and is scaled by filtered rows x positions. `--impl reference` measures a full pass and prints per-partition
+    times next to the filtered rows, so the estimator can be checked."""
     sys.path.insert(0, str(ROOT / "tests"))
     import oracle_bind
     cores = os.cpu_count() or 1
@@ -150,24 +153,29 @@ def cpu_baseline_line(db, query, rows, budget_s=20.0):
     filtered = {p: oracle_bind.filter_cardinality(db, flt, p) for p in db.owned}
     total_filtered = sum(filtered.values())
     order = sorted((p for p in db.owned if filtered[p]), key=lambda p: (p * 2654435761 + 12345) % (1 << 32))
-    sample, t, seen = [], 0.0, 0
+    sample, seen = [], 0
     for p in order:
-        t += oracle_bind.time_query_subset(db, query, [p], faithful=True, threads=cores)[0]
-        seen += filtered[p]
         sample.append(p)
-        if t >= budget_s:
+        seen += filtered[p]
+        if seen >= 0.3 * total_filtered:
             break
-    full = t * total_filtered / max(seen, 1)
+    positions = min(GENOME_LENGTH, 600 * max(cores, 1))      # two chunks of 300 positions per host thread: fewer leave threads idle and over-weigh the fixed costs
+    t = oracle_bind.time_query_sample(db, query, sample, positions, threads=cores)
+    full = t * (total_filtered / max(seen, 1)) * (GENOME_LENGTH / positions)
     fast_s = oracle_bind.time_query_subset(db, query, list(db.owned), faithful=False, threads=cores)[0]
     return {"value": 1.0 / full if full else None, "unit": UNIT, "cores": cores, "kind": "port",
             "best_cpu_algorithm": {"value": 1.0 / fast_s if fast_s else None, "unit": UNIT, "seconds": fast_s,
                                    "note": "NOT the reference's algorithm: the oracle's fast mode (difference array instead of the O(|F| L) contains() loop), whole query, all host threads"},
             "sample": f"oracle faithful mode (the reference's per-position loops, all {cores} host threads), rotation query 0 on {len(sample)} of the {len(order)} partitions the filter selects "
-                      f"({seen} of {total_filtered} filtered rows, {t:.1f} s of CPU work), scaled by filtered rows to {full:.1f} s for the whole {rows}-row query"}
+                      f"({seen} of {total_filtered} filtered rows) and positions 0..{positions} of {GENOME_LENGTH}: {t:.1f} s of CPU work, scaled by filtered rows x positions to {full:.1f} s for the whole {rows}-row query"}
 
 
 def run_reference(args, rank, world):
-    """The reference arm: the CPU restatement of the reference's own algorithm on the host cores (rank 0 only)."""
+    """The reference arm: the CPU restatement of the reference's own algorithm on the host cores (rank 0 only). A whole query
+    takes minutes at 40 M rows, so a step is a bounded sample -- the selected partitions with the fewest filtered rows (at least
+    5 % of them) on the first 300 positions per host thread -- and value = (share of the query the sample is) / (step time),
+    the share being filtered rows x positions (see cpu_baseline_line for the evidence). --full-pass measures the share instead:
+    one pass of the whole query, partition by partition, in set-up."""
     if rank != 0:
         return
     import pysilo
@@ -176,26 +184,44 @@ def run_reference(args, rank, world):
     t0 = time.time()
     db = pysilo.Database.synthetic(args.rows, args.seed)
     query = rotation(db)[0]
-    full, sample, t_sample, cores, per_partition = cpu_calibrate(db, query)
-    fraction = t_sample / full                       # measured share of the whole query's CPU time that the sample is
+    cores = os.cpu_count() or 1
     filtered = {p: oracle_bind.filter_cardinality(db, query["filterExpression"], p) for p in db.owned}
+    total_filtered = sum(filtered.values())
+    sample, seen = [], 0
+    for p in sorted((p for p in db.owned if filtered[p]), key=lambda p: filtered[p]):
+        sample.append(p)
+        seen += filtered[p]
+        if seen >= 0.05 * total_filtered:
+            break
+    positions = min(GENOME_LENGTH, 300 * cores)
+    fraction = (seen / max(total_filtered, 1)) * (positions / GENOME_LENGTH)
+    fraction_source = "filtered rows x positions of the sample / of the query"
+    extra = {}
+    if args.full_pass:
+        full, _, _, _, per_partition = cpu_calibrate(db, query)
+        t_sample = oracle_bind.time_query_sample(db, query, sample, positions, threads=cores)
+        extra = {"full_pass_s": full, "analytic_fraction": fraction,
+                 "per_partition": [{"partition": p, "rows": db.partition_rows(p), "filtered_rows": filtered[p], "cpu_s": round(per_partition[p], 3)} for p in db.owned]}
+        fraction = t_sample / full
+        fraction_source = "measured: sample time / time of one full pass over all partitions"
     setup_s = time.time() - t0
 
     def one_step():
-        return sum(oracle_bind.time_query_subset(db, query, [p], faithful=True, threads=cores)[0] for p in sample)
+        return oracle_bind.time_query_sample(db, query, sample, positions, threads=cores)
     for _ in range(min(args.warmup, 1)):            # a CPU arm needs no more than one warm-up pass
         one_step()
     times = [one_step() for _ in range(args.steps)]
     per_step = sum(times) / len(times)
     value = fraction / per_step                     # whole queries per second
-    sample_text = (f"oracle faithful mode (the reference's per-position loops), all {cores} host threads, rotation query 0; one full pass over all {len(db.owned)} partitions in set-up "
-                   f"took {full:.1f} s; each step = the query on {len(sample)} of {len(db.owned)} partitions = {fraction:.4f} of that time (measured); "
-                   f"value = fraction / step time; the reference itself is not buildable here (DESIGN.md 2)")
+    sample_text = (f"oracle faithful mode (the reference's per-position loops), all {cores} host threads, rotation query 0; each step = the query on {len(sample)} of the "
+                   f"{sum(1 for p in db.owned if filtered[p])} partitions the filter selects ({seen} of {total_filtered} filtered rows), positions 0..{positions} of {GENOME_LENGTH} "
+                   f"= {fraction:.5f} of the query ({fraction_source}); value = share / step time; the reference itself is not buildable here (DESIGN.md 2)")
+    config = {"workload": workload_name(args.rows), "rows": args.rows, "partitions": db.n_partitions, "sample_fraction_of_query": fraction,
+              "note": "queries/s of the host CPU: the same for any --gpus"}
+    config.update(extra)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "strong" if args.gpus > 1 and not args.weak else "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": workload_name(args.rows), "rows": args.rows, "partitions": db.n_partitions, "sample_fraction_of_query": fraction, "full_pass_s": full,
-                       "per_partition": [{"partition": p, "rows": db.partition_rows(p), "filtered_rows": filtered[p], "cpu_s": round(per_partition[p], 3)} for p in db.owned],
-                       "note": "queries/s of the host CPU: the same for any --gpus"},
+            "config": config,
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_text},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "setup_s": round(setup_s, 1)}

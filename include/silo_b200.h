@@ -230,6 +230,23 @@ int sb_group_column_add(sb_db* db, uint32_t partition, const uint32_t* codes, ui
 int sb_aggregated_grouped(sb_db* db, uint32_t n, const uint32_t* partitions, sb_result* const* results, uint32_t n_columns,
                           const uint32_t* group_column_ids, const uint32_t* cardinalities, sb_group_row* rows, size_t capacity, size_t* n_rows);
 
+/* ---- index build: SequenceStorePartition<S>::fill + optimizeBitmaps on the device ---------------------------------
+ * (src/silo/storage/sequence_store.cpp:101-211, position.cpp:24-127). genomes = n_rows * length characters, row-major: the
+ * aligned sequences of one store of one partition as the FASTA reader yields them; present[row] == 0 is a null genome
+ * (sequence_store.cpp:170-176: the row misses every position). char_to_symbol[256] maps a character to its symbol (enum
+ * value) or -1 (then the call fails with the reference's "Illegal character contained in sequence."), iteration_order lists
+ * the symbols as SymbolType::SYMBOLS does (it breaks ties for the most numerous symbol), missing_symbol is N / X.
+ * sb_index_fetch hands back what the host wraps into roaring bitmaps:
+ *   deleted[length]                      most numerous symbol per position (its bitmap is not kept), -1 if no row has a symbol
+ *   slot_off[length * sigma + 1], ids    ascending row ids of bitmap (pos, sym) = ids[slot_off[pos*sigma+sym] .. slot_off[pos*sigma+sym+1])
+ *   missing_off[n_rows + 1], missing_intervals   per row the maximal runs of the missing symbol as (start, end) pairs, end exclusive */
+typedef struct sb_index sb_index;
+int sb_index_build(int device, uint32_t sigma, const int8_t* char_to_symbol, const uint8_t* iteration_order, uint32_t missing_symbol, uint32_t length, uint32_t n_rows,
+                   const char* genomes, const uint8_t* present, sb_index** out);
+int sb_index_sizes(const sb_index* index, uint64_t* n_ids, uint64_t* n_missing_intervals);
+int sb_index_fetch(const sb_index* index, int8_t* deleted, uint64_t* slot_off, uint32_t* ids, uint64_t* missing_off, uint32_t* missing_intervals);
+int sb_index_free(sb_index* index);
+
 /* ---- introspection (mirrors /info?details=true, database.cpp:239-305) -------------------------- */
 typedef struct sb_pool_stats {
    uint64_t array_containers, array_values, run_containers, run_values, run_count, bitset_containers, bitset_values;

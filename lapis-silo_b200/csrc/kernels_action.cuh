@@ -15,29 +15,7 @@
 
 namespace sb {
 
-// tuning knobs of the container scan; the defaults are the measured best (tools/k1_experiment.py builds variants with -D)
-#ifndef SB_K1_THREADS
-#define SB_K1_THREADS 256
-#endif
-#ifndef SB_K1_UNROLL
-#define SB_K1_UNROLL 4
-#endif
-#ifndef SB_K1_PROBE
-#define SB_K1_PROBE 0
-#endif
-#ifndef SB_K1_MIN_CTAS
-#define SB_K1_MIN_CTAS 4
-#endif
-constexpr int K1_THREADS = SB_K1_THREADS;   // 8 warps; up to 4 CTAs per SM (48-57 KB of shared memory each)
-#ifdef SB_K1_TIMELINE
-// diagnostics build only: per-CTA time stamps {smid, start, filter ready, warp 0 out of units, after the barrier, end, units, weight}
-__device__ unsigned long long* g_k1_timeline = nullptr;
-__device__ __forceinline__ unsigned long long globalTimerNs() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-__device__ __forceinline__ uint32_t smId() { uint32_t v; asm volatile("mov.u32 %0, %%smid;" : "=r"(v)); return v; }
-#define K1_STAMP(k) do { if (g_k1_timeline && threadIdx.x == 0) g_k1_timeline[size_t(blockIdx.x) * 8 + (k)] = globalTimerNs(); } while (0)
-#else
-#define K1_STAMP(k) do { } while (0)
-#endif
+constexpr int K1_THREADS = 256;   // 8 warps per CTA of the container scan
 constexpr uint32_t K1_FILTER_BYTES = SLAB_WORDS32 * 4;
 // count table of a tile in shared memory: tile_slots counters + 32 dummy slots (one per lane: where the misses go)
 __host__ __device__ constexpr uint32_t k1TableWords(uint32_t tile_slots) { return (tile_slots + 32 + 1) & ~1u; }
@@ -71,15 +49,7 @@ __device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
 }
 
 // 128-bit load of data that is read once per query
-__device__ __forceinline__ uint4 loadStream(const uint4* p) {
-#ifdef SB_K1_LDG_NOALLOC
-   uint4 v;
-   asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-   return v;
-#else
-   return __ldg(p);
-#endif
-}
+__device__ __forceinline__ uint4 loadStream(const uint4* p) { return __ldg(p); }
 
 // Adds `val` to base[idx] once per distinct idx among the lanes with pred set.
 __device__ __forceinline__ void warpAggregatedSharedAdd(uint32_t* base, uint32_t idx, int val, bool pred) {
@@ -211,9 +181,8 @@ __global__ void k3_init_table(const uint32_t* __restrict__ full_tables, size_t t
 // its flush (all units are counted).
 struct K1Next { WorkItem item; const uint32_t* filter32; uint32_t valid, pad; };
 
-// FLAGS (tuning, compiled side by side): 1 = a hit increments its slot with a predicated reduction (a miss costs no shared-memory
-// operation) instead of every posting incrementing either its slot or the lane's dummy slot; 2 = the directory entry of a
-// warp's next large container is fetched while the current one is counted.
+// FLAGS (compiled side by side): 1 = a hit increments its slot with a predicated reduction (a miss costs no shared-memory
+// operation) instead of every posting incrementing either its slot or the lane's dummy slot.
 template <int UNROLL, int MIN_CTAS, int FLAGS>
 __global__ void __launch_bounds__(K1_THREADS, MIN_CTAS)
 k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int full_mode) {
@@ -325,24 +294,16 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
          for (int t = 0; t < 8; ++t) {
             const uint32_t hit = (w[t] >> (p[t] & 31)) & 1u;
             if (FLAGS & 1) {
+               // (ptxas wraps the predicated reduction in a branch either way; with few hits per warp it still beats the unconditional form)
                asm volatile("{ .reg .pred q; setp.ne.u32 q, %0, 0; @q red.shared.add.u32 [%1], 1; }" ::"r"(hit), "r"(counts_s + ((p[t] >> POSTING_ROW_BITS) << 2)) : "memory");
             } else {
                atomicAdd(&tile_counts[hit ? (p[t] >> POSTING_ROW_BITS) : tile_slots + lane], 1u);   // a miss increments the lane's dummy slot: no branch
             }
          }
       };
-      LargeEntry w_ahead{};
-      if ((FLAGS & 2) && unit < n_large_units) w_ahead = s.large_entries[item.large_begin + (unit >> 1)];
       while (unit < n_units) {
          if (unit < n_large_units) {
-            uint32_t grabbed = 0;
-            LargeEntry w = w_ahead;
-            if (FLAGS & 2) {      // take the next unit now: its directory entry travels while this container is counted
-               grabbed = grab();
-               if (grabbed < n_large_units) w_ahead = s.large_entries[item.large_begin + (grabbed >> 1)];
-            } else {
-               w = s.large_entries[item.large_begin + (unit >> 1)];
-            }
+            const LargeEntry w = s.large_entries[item.large_begin + (unit >> 1)];
             const uint32_t half = unit & 1u;
             const uint4* src = s.large_pool + w.offset16;
             const uint32_t k_kind = w.kind(), k_local = w.keyLocal(), k_size = w.size;
@@ -381,7 +342,7 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
             }
             c2 = warpSum(c2);
             if (lane == 0 && c2 != 0) atomicAdd(&tile_counts[w.slot()], uint32_t(c2));
-            unit = (FLAGS & 2) ? grabbed : grab();
+            unit = grab();
             loadChunk(unit, v);
          } else {
             const uint32_t next = grab();
@@ -465,9 +426,9 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
    const uint32_t* row_off = s.miss_row_off + s.miss_row_base[partition];
    const uint2* iv = s.miss_iv + s.miss_iv_base[partition];
    bool any_row = false;
-   // A warp takes 1,024 rows (32 filter words) at a time and shares the FILTERED rows evenly over its lanes: lane l of round r
-   // owns the (128 r + 32 k + l)-th filtered row of the chunk, k < 4 (found with a search over the lanes' popcount prefix and
-   // __fns), so that every lane has four row_off pairs and then four interval loads in flight whatever the filter looks like.
+   // A thread takes a 32-row word of the filter at a time and walks its set bits four rows at a time: the rows' inline interval
+   // records are eight independent 128-bit loads, nothing depends on another load (the CSR arrays are read only for the few
+   // rows with more intervals than a record holds).
    const uint32_t lane = laneId(), warp = threadIdx.x >> 5;
    const uint32_t word_begin = row0 >> 5, word_end = (row1 + 31) >> 5;
    int at_window_start = 0;      // intervals that begin at the window's first position (leading runs: nearly every row) are counted in a register
@@ -479,30 +440,20 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
          if (hi < w1) atomicAdd(&diff[hi - w0], -1);      // diff[width] is never read
       }
    };
-   for (uint32_t base = word_begin + warp * 32; base < word_end; base += (K2_THREADS / 32) * 32) {
-      const uint32_t word = base + lane;
-      uint32_t bits = word < word_end ? __ldg(q.filter32 + word) : 0u;
-      if (word < word_end && (word + 1) * 32 > row1) bits &= ~0u >> (32 - (row1 & 31));      // row1 is the partition's end here: row blocks are multiples of 32 rows
-      const uint32_t mine = __popc(bits);
-      uint32_t incl = mine;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= uint32_t(d)) incl += t; }
-      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31), excl = incl - mine;
-      if (total) any_row = true;
-      for (uint32_t r0 = 0; r0 < total; r0 += 128) {
-         uint4 rec[4][2];      // the rows' inline interval records: eight 128-bit loads in flight per lane, nothing depends on another load
+   for (uint32_t word = word_begin + threadIdx.x; word < word_end; word += K2_THREADS) {
+      uint32_t bits = __ldg(q.filter32 + word);
+      if ((word + 1) * 32 > row1) bits &= ~0u >> (32 - (row1 & 31));      // row1 is the partition's end here: row blocks are multiples of 32 rows
+      if (bits) any_row = true;
+      while (bits) {
+         uint4 rec[4][2];
          uint32_t rows[4];
 #pragma unroll
          for (int k = 0; k < 4; ++k) {
-            const uint32_t n = r0 + k * 32 + lane, nn = min(n, total - 1);
-            uint32_t owner = 0;      // number of lanes whose inclusive prefix is <= nn = the lane that holds the nn-th filtered row
-#pragma unroll
-            for (uint32_t step = 16; step; step >>= 1) { const uint32_t v = __shfl_sync(0xFFFFFFFFu, incl, owner + step - 1); if (v <= nn) owner += step; }
-            const uint32_t owner_bits = __shfl_sync(0xFFFFFFFFu, bits, owner), owner_excl = __shfl_sync(0xFFFFFFFFu, excl, owner);
             rows[k] = 0xFFFFFFFFu;
             rec[k][0] = rec[k][1] = make_uint4(0, 0, 0, 0);
-            if (n < total) {
-               rows[k] = (base + owner) * 32 + __fns(owner_bits, 0, int(nn - owner_excl) + 1);
+            if (bits) {
+               rows[k] = word * 32 + uint32_t(__ffs(int(bits))) - 1u;
+               bits &= bits - 1u;
                rec[k][0] = __ldg(records + size_t(rows[k]) * 2);
                rec[k][1] = __ldg(records + size_t(rows[k]) * 2 + 1);
             }

@@ -8,9 +8,9 @@
 #include <nccl.h>
 #include "common.cuh"
 #include "kernels_action.cuh"
-#include "kernels_scan2.cuh"
 #include "kernels_filter.cuh"
 #include "kernels_group.cuh"
+#include "kernels_build.cuh"
 #include "pool.cuh"
 
 using namespace sb;
@@ -408,6 +408,7 @@ int sb_column_add(sb_db* db, uint32_t partition, int dtype, const void* values, 
 #include "api_action.inc"
 #include "api_query.inc"
 #include "api_group.inc"
+#include "api_build.inc"
 
 // ---- row selection without any allocation ------------------------------------------------------------------------------
 // For callers that must not reach cudaMalloc (graph capture around them, tight serving loops, harnesses that forbid it):
@@ -475,23 +476,3 @@ extern "C" int sb_mutation_rows_from_table_static(sb_db* db, const char* store_n
       for (size_t i = 0; i < n; ++i) rows[i].symbol = valid[rows[i].symbol];
    });
 }
-
-#ifdef SB_K1_TIMELINE
-// diagnostics build (tools/k1_experiment.py): per-CTA time stamps of the container scan
-extern "C" int sb_debug_timeline_enable(uint32_t max_blocks) {
-   return guarded([&] {
-      unsigned long long* buf = nullptr;
-      SB_CUDA(cudaMalloc(reinterpret_cast<void**>(&buf), size_t(max_blocks) * 64));
-      SB_CUDA(cudaMemset(buf, 0, size_t(max_blocks) * 64));
-      SB_CUDA(cudaMemcpyToSymbol(g_k1_timeline, &buf, sizeof(buf)));
-   });
-}
-extern "C" int sb_debug_timeline_read(uint64_t* out, uint32_t blocks) {
-   return guarded([&] {
-      SB_CUDA(cudaDeviceSynchronize());
-      unsigned long long* buf = nullptr;
-      SB_CUDA(cudaMemcpyFromSymbol(&buf, g_k1_timeline, sizeof(buf)));
-      SB_CUDA(cudaMemcpy(out, buf, size_t(blocks) * 64, cudaMemcpyDeviceToHost));
-   });
-}
-#endif

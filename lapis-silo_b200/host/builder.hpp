@@ -8,6 +8,7 @@
 //   * column fill / null values  src/silo/storage/column/*.cpp
 //   * sequence index fill        src/silo/storage/sequence_store.cpp:101-211, position.cpp:24-127
 #pragma once
+#include <functional>
 #include <algorithm>
 #include <thread>
 
@@ -158,9 +159,12 @@ inline std::vector<std::vector<size_t>> partitionRecords(const std::vector<Input
    return partitions;
 }
 
+// what turns the aligned sequences of one store into its index: fillSequenceStore, or the device build (host/device_build.hpp)
+using StoreFiller = std::function<void(SequenceStorePartition&, const std::vector<const std::optional<std::string>*>&)>;
+
 inline std::unique_ptr<Database> buildDatabase(
    DatabaseConfig config, const std::map<std::string, std::string>& nuc_refs, const std::map<std::string, std::string>& aa_refs,
-   PangoLineageAliasLookup alias, const std::vector<InputRecord>& records
+   PangoLineageAliasLookup alias, const std::vector<InputRecord>& records, const StoreFiller& fill = fillSequenceStore
 ) {
    auto db = std::make_unique<Database>();
    db->config = std::move(config);
@@ -241,7 +245,7 @@ inline std::unique_ptr<Database> buildDatabase(
                auto it = seqs.find(name);
                genomes.push_back(it == seqs.end() ? &null_genome : &it->second);
             }
-            fillSequenceStore(store, genomes);
+            fill(store, genomes);
          }
       }
       db->partitions.push_back(std::move(part));
@@ -274,7 +278,7 @@ inline std::string jsonScalarToString(const json::Value& v) {
 }
 
 // Builds a Database from a directory laid out like the reference's testBaseData/exampleDataset*.
-inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& dir) {
+inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& dir, const StoreFiller& fill = fillSequenceStore) {
    DatabaseConfig config = parseDatabaseConfig(io::readFile(dir + "/database_config.yaml"));
    std::string metadata_file, ndjson_file, alias_file = "pangolineage_alias.json", ref_file = "reference_genomes.json";
    for (const auto& y : io::parseYamlLines(io::readFile(dir + "/preprocessing_config.yaml"))) {
@@ -339,7 +343,7 @@ inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& d
          records.push_back(std::move(rec));
       }
    }
-   return buildDatabase(std::move(config), nuc_refs, aa_refs, std::move(alias), records);
+   return buildDatabase(std::move(config), nuc_refs, aa_refs, std::move(alias), records, fill);
 }
 
 }  // namespace silo::builder

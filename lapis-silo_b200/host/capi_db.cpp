@@ -2,6 +2,7 @@
 // bench.py and __graft_entry__; a C++ host links the headers directly).
 #include "builder.hpp"
 #include "capi_common.hpp"
+#include "device_build.hpp"
 
 using namespace silo;
 
@@ -14,6 +15,37 @@ void* silo_db_build_from_dir(const char* dir) {
    Database* db = nullptr;
    capi::guarded([&] { db = builder::buildDatabaseFromDirectory(dir).release(); });
    return db;
+}
+// the same database with every sequence store built on the device (sb_index_build) instead of builder::fillSequenceStore
+void* silo_db_build_from_dir_device(const char* dir, int device) {
+   Database* db = nullptr;
+   capi::guarded([&] { db = builder::buildDatabaseFromDirectory(dir, builder::deviceStoreFiller(device)).release(); });
+   return db;
+}
+// number of differences between the sequence stores of two databases: bitmaps (set and serialized form), flags, missing-symbol
+// bitmaps, sequence counts; -1 on error
+int64_t silo_db_compare_stores(const void* a_, const void* b_) {
+   int64_t differences = -1;
+   capi::guarded([&] {
+      const auto& a = *static_cast<const Database*>(a_);
+      const auto& b = *static_cast<const Database*>(b_);
+      if (a.partitions.size() != b.partitions.size()) throw std::runtime_error("different numbers of partitions");
+      int64_t diff = 0;
+      for (size_t p = 0; p < a.partitions.size(); ++p) {
+         for (int alphabet_id = 0; alphabet_id < 2; ++alphabet_id) {
+            const auto& stores_b = b.partitions[p]->getSequenceStores(alphabet_id);
+            for (const auto& [name, x] : a.partitions[p]->getSequenceStores(alphabet_id)) {
+               const SequenceStorePartition& y = stores_b.at(name);
+               if (x.sequence_count != y.sequence_count || x.bitmaps.size() != y.bitmaps.size() || x.missing_symbol_bitmaps.size() != y.missing_symbol_bitmaps.size()) { ++diff; continue; }
+               for (size_t k = 0; k < x.bitmaps.size(); ++k) if (!(x.bitmaps[k] == y.bitmaps[k]) || x.bitmaps[k].toPortable() != y.bitmaps[k].toPortable()) ++diff;
+               for (size_t k = 0; k < x.deleted.size(); ++k) if (x.deleted[k] != y.deleted[k] || x.flipped[k] != y.flipped[k]) ++diff;
+               for (size_t k = 0; k < x.missing_symbol_bitmaps.size(); ++k) if (x.missing_symbol_bitmaps[k].toPortable() != y.missing_symbol_bitmaps[k].toPortable()) ++diff;
+            }
+         }
+      }
+      differences = diff;
+   });
+   return differences;
 }
 void silo_db_free(void* db) { delete static_cast<Database*>(db); }
 uint32_t silo_db_partition_count(const void* db) { return static_cast<uint32_t>(static_cast<const Database*>(db)->partitions.size()); }

@@ -1,5 +1,6 @@
 // C entry points of the synthetic dataset generator for ctypes.
 #include "capi_common.hpp"
+#include "device_build.hpp"
 #include "synth.hpp"
 
 using namespace silo;
@@ -45,9 +46,13 @@ const char* silo_synth_lineage_name(void* handle, uint32_t i) { return static_ca
 // Rebuilds the database from the explicit row strings through the reference-shaped builder
 // (builder::fillSequenceStore) and compares every bitmap and flag with the generated index.
 // Returns the number of differences (0 = identical), or -1 on error.
-int64_t silo_synth_verify_against_builder(void* handle_) {
+// device < 0: builder::fillSequenceStore on the host; otherwise the device build (sb_index_build) on that GPU.
+int64_t silo_synth_verify_against_builder_on(void* handle_, int device);
+int64_t silo_synth_verify_against_builder(void* handle_) { return silo_synth_verify_against_builder_on(handle_, -1); }
+int64_t silo_synth_verify_against_builder_on(void* handle_, int device) {
    int64_t differences = -1;
    capi::guarded([&] {
+      const builder::StoreFiller fill = device < 0 ? builder::StoreFiller(builder::fillSequenceStore) : builder::deviceStoreFiller(device);
       auto& g = static_cast<SynthHandle*>(handle_)->generated;
       if (g.explicit_sequences.empty()) throw std::runtime_error("generated without explicit_sequences");
       int64_t diff = 0;
@@ -58,7 +63,7 @@ int64_t silo_synth_verify_against_builder(void* handle_) {
                rebuilt.init(store.alphabet, store.reference_sequence);
                std::vector<const std::optional<std::string>*> genomes;
                for (const auto& s : g.explicit_sequences[p].at(name)) genomes.push_back(&s);
-               builder::fillSequenceStore(rebuilt, genomes);
+               fill(rebuilt, genomes);
                if (rebuilt.sequence_count != store.sequence_count) ++diff;
                for (size_t k = 0; k < store.bitmaps.size(); ++k) if (!(rebuilt.bitmaps[k] == store.bitmaps[k]) || rebuilt.bitmaps[k].toPortable() != store.bitmaps[k].toPortable()) ++diff;
                for (size_t k = 0; k < store.deleted.size(); ++k) if (rebuilt.deleted[k] != store.deleted[k] || rebuilt.flipped[k] != store.flipped[k]) ++diff;

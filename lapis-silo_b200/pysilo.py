@@ -42,6 +42,8 @@ def host():
         "silo_last_error": (cp, []),
         "silo_free": (None, [vp]),
         "silo_db_build_from_dir": (vp, [cp]),
+        "silo_db_build_from_dir_device": (vp, [cp, ctypes.c_int]),
+        "silo_db_compare_stores": (ctypes.c_int64, [vp, vp]),
         "silo_db_free": (None, [vp]),
         "silo_db_partition_count": (u32, [vp]),
         "silo_db_partition_rows": (u32, [vp, u32]),
@@ -82,6 +84,7 @@ def host():
         "silo_synth_clade_mutation": (None, [vp, u32, pu32, ctypes.c_char_p]),
         "silo_synth_lineage_name": (cp, [vp, u32]),
         "silo_synth_verify_against_builder": (ctypes.c_int64, [vp]),
+        "silo_synth_verify_against_builder_on": (ctypes.c_int64, [vp, ctypes.c_int]),
         "silo_test_worker_pool": (ctypes.c_int64, [u32, u32, u32, ctypes.c_int32]),
         "silo_literal_create": (vp, []),
         "silo_literal_free": (None, [vp]),
@@ -151,6 +154,21 @@ class Database:
         return cls(h)
 
     @classmethod
+    def from_directory_device_build(cls, path, device=0):
+        """the same database with every sequence store built on the GPU (sb_index_build) instead of the host builder"""
+        h = host().silo_db_build_from_dir_device(str(path).encode(), device)
+        if not h:
+            raise _error()
+        return cls(h)
+
+    def store_differences(self, other):
+        """number of differing bitmaps / flags / missing-symbol bitmaps between the sequence stores of two databases"""
+        d = host().silo_db_compare_stores(self.handle, other.handle)
+        if d < 0:
+            raise _error()
+        return d
+
+    @classmethod
     def synthetic(cls, n_sequences, seed, with_amino_acids=False, explicit_sequences=False, genome_length=0, n_threads=0,
                   reference_genomes=None, world=1, rank=0):
         ref = reference_genomes or ROOT / "tests" / "golden" / "exampleDataset1000Sequences" / "reference_genomes.json"
@@ -184,8 +202,10 @@ class Database:
     def lineage_names(self):
         return [host().silo_synth_lineage_name(self._owner, i).decode() for i in range(96)]
 
-    def verify_against_builder(self):
-        d = host().silo_synth_verify_against_builder(self._owner)
+    def verify_against_builder(self, device=-1):
+        """rebuilds every store from the explicit row strings -- on the host (device < 0) or with the device index build -- and
+        counts the differences to the generated index"""
+        d = host().silo_synth_verify_against_builder_on(self._owner, device)
         if d < 0:
             raise _error()
         return d

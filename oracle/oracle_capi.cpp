@@ -59,6 +59,18 @@ double oracle_time_query_subset(const void* db, const char* query_json, int fait
    return seconds;
 }
 
+// the same on positions [0, position_limit) only (faithful mode; the result rows are not meaningful): bench.py's bounded CPU sample
+double oracle_time_query_sample(const void* db, const char* query_json, int threads, const uint32_t* partitions, uint32_t n, uint32_t position_limit) {
+   double seconds = -1;
+   guarded([&] {
+      oracle::Options options{true, static_cast<unsigned>(threads), std::vector<uint32_t>(partitions, partitions + n), position_limit};
+      const auto begin = std::chrono::steady_clock::now();
+      oracle::executeQuery(*static_cast<const silo::Database*>(db), query_json, options);
+      seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - begin).count();
+   });
+   return seconds;
+}
+
 int oracle_eval_optree(const char* optree_json, uint32_t** ids, size_t* n) {
    return guarded([&] {
       auto holder = silo::opTreeFromJson(optree_json);

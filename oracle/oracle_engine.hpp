@@ -235,8 +235,11 @@ inline void addStoreFast(const FilterAndStore& fs, bool full, uint32_t* counts, 
 }
 
 // mutations.cpp:139-164: positions split in chunks of 300 over a thread pool (TBB in the reference)
-inline std::vector<uint32_t> calculateMutationsPerPosition(const Alphabet& alphabet, size_t length, const PrefilteredBitmaps& pre, bool faithful, unsigned n_threads) {
+// `position_limit` (bounded CPU samples of bench.py): faithful mode walks positions [0, limit) only; 0 = all
+inline std::vector<uint32_t> calculateMutationsPerPosition(const Alphabet& alphabet, size_t length, const PrefilteredBitmaps& pre, bool faithful, unsigned n_threads,
+                                                           uint32_t position_limit = 0) {
    std::vector<uint32_t> counts(size_t(alphabet.count) * length, 0);
+   const uint32_t walk = position_limit ? std::min<uint32_t>(position_limit, static_cast<uint32_t>(length)) : static_cast<uint32_t>(length);
    if (n_threads == 0) n_threads = std::max(1u, std::thread::hardware_concurrency());
    if (faithful) {
       constexpr uint32_t POSITIONS_PER_PROCESS = 300;
@@ -244,8 +247,8 @@ inline std::vector<uint32_t> calculateMutationsPerPosition(const Alphabet& alpha
       auto worker = [&] {
          while (true) {
             const uint32_t begin = next.fetch_add(POSITIONS_PER_PROCESS);
-            if (begin >= length) break;
-            const uint32_t end = std::min<uint32_t>(begin + POSITIONS_PER_PROCESS, static_cast<uint32_t>(length));
+            if (begin >= walk) break;
+            const uint32_t end = std::min<uint32_t>(begin + POSITIONS_PER_PROCESS, walk);
             for (uint32_t pos = begin; pos < end; ++pos) {
                addPositionForMixedBitmaps(pos, pre, counts.data(), length, alphabet);
                addPositionForFullBitmaps(pos, pre, counts.data(), length, alphabet);
@@ -311,6 +314,7 @@ struct Options {
    bool faithful = true;
    unsigned threads = 0;
    std::vector<uint32_t> partitions;   // bounded samples: evaluate only these partitions (empty = all), the others count as empty filters
+   uint32_t position_limit = 0;        // bounded samples: faithful Mutations walks positions [0, limit) only (0 = all)
 };
 
 // query_engine.cpp:40-49: serial compile + evaluate per partition
@@ -345,7 +349,7 @@ inline QueryResult executeMutations(const Database& db, const Action& action, st
       const auto& reference = references.at(name);
       auto it = pre.find(name);
       if (it == pre.end()) continue;
-      auto counts = calculateMutationsPerPosition(alphabet, reference.size(), it->second, options.faithful, options.threads);
+      auto counts = calculateMutationsPerPosition(alphabet, reference.size(), it->second, options.faithful, options.threads, options.position_limit);
       addMutationsToOutput(name, alphabet, reference, counts, action.min_proportion, result.query_result);
       if (tables) (*tables)[name] = std::move(counts);
    }

@@ -100,6 +100,18 @@ def time_query_subset(db, query, partitions, faithful=True, threads=0):
     return seconds, rows.value
 
 
+def time_query_sample(db, query, partitions, position_limit, threads=0):
+    """seconds of the faithful CPU restatement for `query` on `partitions`, positions [0, position_limit) only"""
+    arr = (ctypes.c_uint32 * max(len(partitions), 1))(*partitions)
+    fn = lib().oracle_time_query_sample
+    fn.restype = ctypes.c_double
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, ctypes.c_uint32]
+    seconds = fn(db.handle, json.dumps(query).encode(), threads, arr, len(partitions), position_limit)
+    if seconds < 0:
+        raise _err()
+    return seconds
+
+
 def mutation_counts_subset(db, query, sequence_name, table_len, partitions, faithful=True, threads=0):
     """the table of `query` restricted to `partitions` (the others count as empty filters)"""
     arr = (ctypes.c_uint32 * max(len(partitions), 1))(*partitions)

@@ -235,13 +235,12 @@ def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
 
 @pytest.mark.parametrize("env", [{"SB_K1_CTAS": "1"}, {"SB_K1_CTAS": "3"}, {"SB_K1_CTAS": "7"}, {"SB_K1_CTAS": "4000"}, {"SB_ITEM_CAP_KB": "4"},
                                  {"SB_RUN_CAP_KB": "1"}, {"SB_RUN_CAP_KB": "4096"}, {"SB_TILE_POSITIONS": "512"},
-                                 {"SB_K1_VARIANT": "1"}, {"SB_K1_VARIANT": "2"}, {"SB_K1_VARIANT": "4", "SB_K1_CTAS": "5"}, {"SB_K1_VARIANT": "6", "SB_ITEM_CAP_KB": "4"},
-                                 {"SB_K1_VARIANT": "7", "SB_TILE_POSITIONS": "512"}],
+                                 {"SB_K1_VARIANT": "1"}, {"SB_K1_VARIANT": "2", "SB_K1_CTAS": "5"}, {"SB_K1_VARIANT": "2", "SB_TILE_POSITIONS": "512", "SB_ITEM_CAP_KB": "4"}],
                          ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
 def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch):
     """the container scan with odd numbers of persistent CTAs (one CTA takes every item, more CTAs than items), with tiny work
     items (many items per segment), one item or a whole slab per run, 512-position tiles, and in its other compiled shapes
-    (k1_scan without predicated increments, k1_pipe at several depths), against the oracle"""
+    (without predicated increments, two posting loads in flight at 4 CTAs per SM), against the oracle"""
     pysilo, oracle = libs
     for k, v in env.items():
         monkeypatch.setenv(k, v)      # read when the device database is created

@@ -37,21 +37,18 @@ def measure(pysilo, torch, engine, db, name, query, rows, device_table=None, cal
             "e2e_ms_median": statistics.median(lat), "e2e_ms_p99": lat[min(len(lat) - 1, int(0.99 * len(lat)))], "e2e_queries_per_s": 1e3 / statistics.median(lat),
             "result_rows": len(json.loads(body)["queryResult"]), "response_bytes": len(body),
             "pool": {k: stats[k] for k in ("array_containers", "run_containers", "bitset_containers", "payload_bytes", "missing_bytes", "total_device_bytes")}}
-    if device_table:       # (sequence index, table length): device-resident replay of filter + count table, CUDA events
-        index, table_len = device_table
-        counts = torch.zeros(table_len, dtype=torch.int32, device="cuda:0")
+    if device_table:       # device-resident replay of the prepared query (one CUDA graph launch), CUDA events on its stream
         prepared = pysilo.Prepared(engine, query)
-        info = prepared.run_device(index, counts.data_ptr(), table_len, want_bytes=True)
         for _ in range(3):
-            prepared.run_device(index, counts.data_ptr(), table_len)
-        pysilo.k1_accumulated(engine, reset=True)
-        pysilo.timer_begin(engine)
+            prepared.run_device()
+        samples = []
         for _ in range(calls):
-            prepared.run_device(index, counts.data_ptr(), table_len)
-        ms = pysilo.timer_end(engine) / calls
-        k1_ms, n = pysilo.k1_accumulated(engine, reset=True)
-        line.update({"device_ms_per_query": ms, "device_queries_per_s": 1e3 / ms, "algorithmic_bytes": info["alg_bytes"], "scan_gb_per_s": info["alg_bytes"] / ms / 1e6,
-                     "k1_ms_in_step": k1_ms / max(n, 1), "k1_algorithmic_bytes": info["k1_bytes"]})
+            prepared.run_device()
+            samples.append(prepared.elapsed_ms())
+        ms = statistics.median(samples)
+        info = prepared.algorithmic_bytes(device_table[0])
+        line.update({"device_ms_per_query": ms, "device_queries_per_s": 1e3 / ms, "algorithmic_bytes": info["alg_bytes"], "k1_algorithmic_bytes": info["k1_bytes"],
+                     "scan_gb_per_s": info["alg_bytes"] / ms / 1e6 if info["k1_bytes"] else None})      # no scan rate for pure table hits (full partitions: precomputed tables)
         prepared.close()
     print(json.dumps(line), flush=True)
     return body
