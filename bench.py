@@ -3,6 +3,9 @@
 
 Workload: ONE database of --rows (default 40 M) synthetic sequences x 29,903 nt in lineage DatabasePartitions
 (seed 0x51100005), sharded over the N ranks by DatabasePartition (strong scaling: N = 1 holds all of it, 4 GB of index).
+For N > 1 the database is the same rows and values; by default every lineage partition is cut into N DatabasePartitions of
+consecutive rows, one per GPU, so that every GPU holds 1/N of every lineage whatever the filter selects (--shard partitions
+keeps the 23 whole partitions and assigns them by size: a filter that selects 7 of them leaves most GPUs idle).
 One "step" = one nucleotide Mutations query (minProportion 0.05) out of a rotation of 8 distinct N-Of(3 of 10) filters over
 clade-defining NucleotideEquals (different picks -> different sets of partial partitions, different |F|); step i runs
 query i mod 8. For N > 1 every rank answers the query on its partitions and the count tables are summed inside the query's
@@ -51,6 +54,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--full-pass", action="store_true", help="--impl reference: measure the sample's share of the query by one full pass of the CPU restatement (minutes at 40 M rows)")
     ap.add_argument("--weak", action="store_true", help="N > 1: every rank holds its own shard of --rows sequences (replicated shards) instead of a share of one database")
+    ap.add_argument("--shard", default="rows", choices=["rows", "partitions"],
+                    help="N > 1, one database: 'rows' cuts every lineage partition into N DatabasePartitions of consecutive rows, one per GPU (every GPU holds 1/N of every lineage); "
+                         "'partitions' assigns the 23 whole lineage partitions to the GPUs (longest-processing-time-first on rows)")
     ap.add_argument("--lineage", action="store_true", help="also measure the C5 lineage and True queries (full / partial / empty partitions)")
     ap.add_argument("--in-flight", type=int, default=8, help="queries in flight of the extra throughput measurement (N = 1 only; 0 = skip)")
     return ap.parse_args()
@@ -257,7 +263,8 @@ def main():
     t0 = time.time()
     weak = world > 1 and args.weak
     units_per_step = world if weak else 1          # weak: every rank answers the query on a shard of its own
-    db = pysilo.Database.synthetic(args.rows, args.seed + rank) if weak else pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank)
+    slices = world if (world > 1 and not weak and args.shard == "rows") else 1
+    db = pysilo.Database.synthetic(args.rows, args.seed + rank) if weak else pysilo.Database.synthetic(args.rows, args.seed, world=world, rank=rank, row_slices=slices)
     total_rows = args.rows * (world if weak else 1)
     t_generate = time.time() - t0
     engine = pysilo.Engine(db, local_rank, db.owned)
@@ -453,7 +460,9 @@ def main():
             "config": {"workload": workload_name(args.rows), "rows": total_rows, "partitions": db.n_partitions * (world if weak else 1), "partitions_on_rank0": len(db.owned),
                        "l2": "inputs larger than L2 (container pool streamed once per query; 8 different queries in rotation)",
                        "parallelism": (f"{world} replicated shard(s) of {args.rows} sequences (seed + rank), one per GPU" if weak else
-                                       f"one database of {args.rows} sequences, DatabasePartitions sharded over {world} GPU(s), NCCL reduce of the valid-symbol rows of the count table inside the query's submission")},
+                                       f"one database of {args.rows} sequences, " + (f"every lineage partition cut into {world} DatabasePartitions of consecutive rows, one per GPU" if slices > 1 else f"whole lineage DatabasePartitions assigned to {world} GPU(s) by rows (LPT)") +
+                                       ", NCCL reduce of the valid-symbol rows of the count table inside the query's submission"),
+                       "shard": args.shard if world > 1 and not weak else None},
             "e2e": {"value": units_per_step * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (h2d1 - h2d0) // args.steps + sum(len(t) for t in texts) // len(texts),
                     "d2h_bytes_per_step": (d2h1 - d2h0) // args.steps, "ms_per_step": e2e_s * 1e3 / args.steps, "plan_cache": "off",
                     "cached": {"value": args.steps / e2e_cached_s, "ms_per_step": e2e_cached_s * 1e3 / args.steps, "note": "query text -> prepared query (CUDA graph) in the engine's plan cache"} if e2e_cached_s else None},

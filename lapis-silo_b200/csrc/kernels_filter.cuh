@@ -124,7 +124,7 @@ __global__ void build_miss_tiles(const uint32_t* __restrict__ row_off, const uin
 // dependent loads of the interval search (sorted, disjoint intervals: binary search) are few rounds with many loads in flight.
 // Every 32-bit word of the leaf's scratch bitset (an even number of them) is written: the scratch area is never zeroed.
 constexpr uint32_t BSEL_ROWS = 32;     // rows per thread
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 6)
 leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict__ jobs, uint64_t* __restrict__ scratch) {
    __shared__ uint32_t cand_rows[8][1024];
    __shared__ uint32_t found_words[8][32];
@@ -152,19 +152,19 @@ leaf_bitmap_selection(const SeqDev* __restrict__ seqs, const BselJob* __restrict
       const uint32_t* row_off = s.miss_row_off + s.miss_row_base[job.partition];
       const uint2* iv = s.miss_iv + s.miss_iv_base[job.partition];
       const uint4* records = s.miss_inline + s.miss_inline_base[job.partition] * 2;
-      // four candidates per lane at a time: their inline interval records are eight independent 128-bit loads; only a row with
+      // two candidates per lane at a time (a warp of 1,024 rows rarely has more than 64): their inline interval records are four independent 128-bit loads; only a row with
       // more intervals than a record holds (all words set) is searched in the CSR arrays
-      for (uint32_t k0 = lane; k0 < total; k0 += 128) {
-         uint32_t row[4];
-         uint4 rec[4][2];
+      for (uint32_t k0 = lane; k0 < total; k0 += 64) {
+         uint32_t row[2];
+         uint4 rec[2][2];
 #pragma unroll
-         for (uint32_t q = 0; q < 4; ++q) {
+         for (uint32_t q = 0; q < 2; ++q) {
             row[q] = 0xFFFFFFFFu;
             rec[q][0] = rec[q][1] = make_uint4(0, 0, 0, 0);
             if (k0 + q * 32 < total) { row[q] = cand_rows[warp][k0 + q * 32]; rec[q][0] = __ldg(records + size_t(row[q]) * 2); rec[q][1] = __ldg(records + size_t(row[q]) * 2 + 1); }
          }
 #pragma unroll
-         for (uint32_t q = 0; q < 4; ++q) {
+         for (uint32_t q = 0; q < 2; ++q) {
             if (row[q] == 0xFFFFFFFFu) continue;
             const uint32_t w[8] = {rec[q][0].x, rec[q][0].y, rec[q][0].z, rec[q][0].w, rec[q][1].x, rec[q][1].y, rec[q][1].z, rec[q][1].w};
             bool found = false;
@@ -305,6 +305,7 @@ struct LeafRes {
 };
 static_assert(sizeof(LeafRes) == 32, "LeafRes must be 32 bytes");
 constexpr uint32_t EVAL_RES_WINDOW = 64;
+constexpr uint32_t EVAL_PROG_SMEM = 768;      // program words kept in shared memory (a 10-leaf N-Of is about 120)
 
 __device__ __forceinline__ LeafRes resolveLeaf(const EvalArgs& a, const LeafDesc& leaf, uint32_t chunk) {
    LeafRes r{nullptr, RES_NONE, 0, 0, 0, 0, 0};
@@ -352,6 +353,7 @@ eval_plans(const EvalArgs a) {
    extern __shared__ __align__(16) uint64_t eval_smem[];
    __shared__ int warp_sums[EVAL_PER_THREAD][EVAL_THREADS / 32];
    __shared__ LeafRes res[EVAL_RES_WINDOW];
+   __shared__ uint32_t prog_s[EVAL_PROG_SMEM];
    const PlanDesc plan = a.plans[blockIdx.y];
    const uint32_t chunk = blockIdx.x, w_base = chunk * EVAL_WORDS, tid = threadIdx.x;
    if (w_base >= plan.n_words_padded) return;
@@ -365,15 +367,23 @@ eval_plans(const EvalArgs a) {
 #pragma unroll
       for (int j = 0; j < EVAL_PER_THREAD; ++j) staging64[j * EVAL_THREADS + tid] = 0;     // invariant: all zero between leaves
       __syncthreads();
+      // the program: in shared memory when it fits (every operand fetch from global memory is a dependent load in front of the op)
       const uint32_t* pc = a.programs + plan.prog_off;
+      if (plan.prog_len <= EVAL_PROG_SMEM) {
+         for (uint32_t i = tid; i < plan.prog_len; i += EVAL_THREADS) prog_s[i] = __ldg(pc + i);
+         pc = prog_s;
+         __syncthreads();
+      }
       const uint32_t* end = pc + plan.prog_len;
+      uint64_t ahead[EVAL_PER_THREAD];      // the words of the NEXT leaf when they can be read in place: issued while this leaf's operator runs
+      uint32_t ahead_leaf = 0xFFFFFFFFu;
       const LeafDesc* leaves = a.leaves + plan.leaf_off;
       int sp = 0;      // entries on the stack: levels 0 .. sp-2 in `stk`, the top in `tos`
       uint32_t res_begin = 0, res_end = 0;      // leaves [res_begin, res_end) of the plan are resolved in `res` (leaves are numbered in program order)
 #define SB_LEVEL(l, j) stk[size_t(l) * EVAL_WORDS + (j) * EVAL_THREADS + tid]
 #define SB_SPILL() do { if (sp > 0) { _Pragma("unroll") for (int j = 0; j < EVAL_PER_THREAD; ++j) SB_LEVEL(sp - 1, j) = tos[j]; } ++sp; } while (0)
       while (pc < end) {
-         const uint32_t op = __ldg(pc++);
+         const uint32_t op = (*pc++);
          switch (op) {
             case P_ZERO:
                SB_SPILL();
@@ -381,12 +391,12 @@ eval_plans(const EvalArgs a) {
                for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
                break;
             case P_RANGES: {
-               const uint32_t n = __ldg(pc++);
+               const uint32_t n = (*pc++);
                SB_SPILL();
 #pragma unroll
                for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
                for (uint32_t k = 0; k < n; ++k) {
-                  const uint32_t r0 = __ldg(pc), r1 = __ldg(pc + 1);
+                  const uint32_t r0 = pc[0], r1 = pc[1];
                   pc += 2;
 #pragma unroll
                   for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] |= rangeMask(w_base + j * EVAL_THREADS + tid, r0, r1);
@@ -394,7 +404,7 @@ eval_plans(const EvalArgs a) {
                break;
             }
             case P_LEAF: {
-               const uint32_t li = __ldg(pc++);
+               const uint32_t li = (*pc++);
                if (li >= res_end || li < res_begin) {      // uniform over the CTA: resolve the next window of leaves, one thread per leaf
                   __syncthreads();
                   if (tid < EVAL_RES_WINDOW && li + tid < plan.n_leaves) res[tid] = resolveLeaf(a, leaves[li + tid], chunk);
@@ -406,9 +416,14 @@ eval_plans(const EvalArgs a) {
 #pragma unroll
                for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = 0;
                if (r.mode == RES_DIRECT) {
-                  const uint64_t* direct = static_cast<const uint64_t*>(r.ptr);
+                  if (ahead_leaf == li) {
 #pragma unroll
-                  for (int j = 0; j < EVAL_PER_THREAD; ++j) if (uint32_t(j * EVAL_THREADS + tid) < r.size) tos[j] = __ldg(direct + j * EVAL_THREADS + tid);
+                     for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = ahead[j];
+                  } else {
+                     const uint64_t* direct = static_cast<const uint64_t*>(r.ptr);
+#pragma unroll
+                     for (int j = 0; j < EVAL_PER_THREAD; ++j) if (uint32_t(j * EVAL_THREADS + tid) < r.size) tos[j] = __ldg(direct + j * EVAL_THREADS + tid);
+                  }
                } else if (r.mode != RES_NONE) {      // uniform over the CTA
                   if (r.mode == RES_CONTAINER) {
                      stageContainer(staging, r.e_begin, r.size, static_cast<const uint16_t*>(r.ptr));
@@ -429,10 +444,17 @@ eval_plans(const EvalArgs a) {
                   for (int j = 0; j < EVAL_PER_THREAD; ++j) { tos[j] = staging64[j * EVAL_THREADS + tid]; staging64[j * EVAL_THREADS + tid] = 0; }
                   __syncthreads();
                }
+               if (li + 1 < res_end && li + 1 < plan.n_leaves && res[li + 1 - res_begin].mode == RES_DIRECT) {      // leaves are numbered in program order
+                  const LeafRes nx = res[li + 1 - res_begin];
+                  const uint64_t* direct = static_cast<const uint64_t*>(nx.ptr);
+#pragma unroll
+                  for (int j = 0; j < EVAL_PER_THREAD; ++j) ahead[j] = uint32_t(j * EVAL_THREADS + tid) < nx.size ? __ldg(direct + j * EVAL_THREADS + tid) : 0ull;
+                  ahead_leaf = li + 1;
+               }
                break;
             }
             case P_NOT: {   // flip(0, row_count)
-               const uint32_t rc = __ldg(pc++);
+               const uint32_t rc = (*pc++);
 #pragma unroll
                for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] ^= rangeMask(w_base + j * EVAL_THREADS + tid, 0, rc);
                break;
@@ -453,7 +475,7 @@ eval_plans(const EvalArgs a) {
                for (int j = 0; j < EVAL_PER_THREAD; ++j) tos[j] = SB_LEVEL(sp - 1, j) & ~tos[j];
                break;
             case P_THR_INIT: {
-               const uint32_t d = __ldg(pc++);
+               const uint32_t d = (*pc++);
                for (uint32_t k = 0; k < d; ++k) {
                   SB_SPILL();
 #pragma unroll
@@ -462,8 +484,8 @@ eval_plans(const EvalArgs a) {
                break;
             }
             case P_THR_ADD: {   // threshold.cpp:92-129, one child; plane j = rows matching >= j + 1 children so far
-               const int d = int(__ldg(pc)), i = int(__ldg(pc + 1)), n = int(__ldg(pc + 2)), k = int(__ldg(pc + 3));
-               const uint32_t negated = __ldg(pc + 4), rc = __ldg(pc + 5);
+               const int d = int(pc[0]), i = int(pc[1]), n = int(pc[2]), k = int(pc[3]);
+               const uint32_t negated = pc[4], rc = pc[5];
                pc += 6;
                --sp;                              // the child is in `tos`; the d planes are levels sp-d .. sp-1, all in `stk`
                const int base = sp - d;
@@ -478,8 +500,8 @@ eval_plans(const EvalArgs a) {
                break;
             }
             case P_THR_FIN: {
-               const int d = int(__ldg(pc)), n = int(__ldg(pc + 1));
-               const uint32_t exact = __ldg(pc + 2);
+               const int d = int(pc[0]), n = int(pc[1]);
+               const uint32_t exact = pc[2];
                pc += 3;
                const int base = sp - d;           // top plane in `tos`, the others in levels base .. sp-2
 #pragma unroll

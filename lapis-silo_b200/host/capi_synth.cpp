@@ -16,7 +16,7 @@ extern "C" {
 // reference_genomes_json: path of a reference_genomes.json (testBaseData layout). Returns a handle
 // owning the Database; silo_synth_db() yields the Database* usable with silo_engine_create / oracle_*.
 void* silo_synth_generate(const char* reference_genomes_json, uint64_t n_sequences, uint64_t seed, int with_amino_acids,
-                          int explicit_sequences, uint32_t genome_length, uint32_t n_threads, uint32_t world, uint32_t rank) {
+                          int explicit_sequences, uint32_t genome_length, uint32_t n_threads, uint32_t world, uint32_t rank, uint32_t row_slices) {
    SynthHandle* handle = nullptr;
    capi::guarded([&] {
       std::map<std::string, std::string> nuc, aa;
@@ -24,7 +24,7 @@ void* silo_synth_generate(const char* reference_genomes_json, uint64_t n_sequenc
       if (nuc.count("main")) { std::string main = nuc["main"]; nuc.clear(); nuc["main"] = main; }
       synth::Options options;
       options.n_sequences = n_sequences; options.seed = seed; options.with_amino_acids = with_amino_acids != 0;
-      options.explicit_sequences = explicit_sequences != 0; options.genome_length = genome_length; options.n_threads = n_threads; options.world = world ? world : 1; options.rank = rank;
+      options.explicit_sequences = explicit_sequences != 0; options.genome_length = genome_length; options.n_threads = n_threads; options.world = world ? world : 1; options.rank = rank; options.row_slices = row_slices ? row_slices : 1;
       auto h = std::make_unique<SynthHandle>();
       h->generated = synth::generate(options, nuc, aa);
       handle = h.release();

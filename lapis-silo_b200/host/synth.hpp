@@ -47,6 +47,8 @@ struct Options {
    uint32_t n_threads = 0;
    uint32_t genome_length = 0;        // 0 = full reference; otherwise truncate (tests)
    uint32_t world = 1, rank = 0;      // multi-GPU: build only the partitions this rank owns (the others stay empty shells)
+   uint32_t row_slices = 1;           // every lineage partition is cut into this many DatabasePartitions of consecutive rows (same
+                                      // rows, same values: a finer horizontal split, so that N GPUs can share every lineage evenly)
 };
 
 struct Event { uint32_t pos; uint8_t sym; };

@@ -220,6 +220,26 @@ inline Generated generate(const Options& options, const std::map<std::string, st
    std::vector<std::vector<RowMeta>> partition_rows(n_partitions);
    for (const auto& m : metas) partition_rows[partition_of_rank[order_of_lineage[m.lineage]]].push_back(m);
    std::vector<RowMeta>().swap(metas);
+   if (options.row_slices > 1) {      // row order inside a lineage partition (date, id) first, then consecutive slices become partitions of their own
+      {
+         std::atomic<uint32_t> next{0};
+         std::vector<std::thread> sorters;
+         for (unsigned t = 0; t < std::min<unsigned>(n_threads, n_partitions); ++t) sorters.emplace_back([&] {
+            for (uint32_t p; (p = next.fetch_add(1)) < n_partitions;) {
+               std::sort(partition_rows[p].begin(), partition_rows[p].end(), [](const RowMeta& a, const RowMeta& b) { return a.date != b.date ? a.date < b.date : a.id < b.id; });
+            }
+         });
+         for (auto& th : sorters) th.join();
+      }
+      std::vector<std::vector<RowMeta>> pieces;
+      for (auto& rows : partition_rows) {
+         const uint64_t n = rows.size();
+         for (uint32_t k = 0; k < options.row_slices; ++k) pieces.emplace_back(rows.begin() + n * k / options.row_slices, rows.begin() + n * (k + 1) / options.row_slices);
+         std::vector<RowMeta>().swap(rows);
+      }
+      partition_rows.swap(pieces);
+      n_partitions = static_cast<uint32_t>(partition_rows.size());
+   }
 
    // dictionaries are shared by all partitions: fill them before the parallel phase
    static const char* const REGIONS[6] = {"Africa", "Asia", "Europe", "North America", "Oceania", "South America"};
@@ -237,7 +257,8 @@ inline Generated generate(const Options& options, const std::map<std::string, st
       std::stable_sort(by_size.begin(), by_size.end(), [&](uint32_t a, uint32_t b) { return partition_rows[a].size() > partition_rows[b].size(); });
       std::vector<uint64_t> load(std::max<uint32_t>(options.world, 1), 0);
       for (uint32_t p : by_size) {
-         const uint32_t r = static_cast<uint32_t>(std::min_element(load.begin(), load.end()) - load.begin());
+         uint32_t r = static_cast<uint32_t>(std::min_element(load.begin(), load.end()) - load.begin());
+         if (options.row_slices > 1 && options.row_slices % std::max<uint32_t>(options.world, 1) == 0) r = (p % options.row_slices) % options.world;   // slice k of every lineage -> rank k mod world
          rank_of_partition[p] = r;
          load[r] += partition_rows[p].size();
       }

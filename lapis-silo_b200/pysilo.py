@@ -75,7 +75,7 @@ def host():
         "silo_prepared_elapsed_ms": (ctypes.c_float, [vp]),
         "silo_engine_set_plan_cache": (None, [vp, ctypes.c_int]),
         "silo_engine_execute_sharded": (vp, [vp, cp, ctypes.c_int]),
-        "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32]),
+        "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32, u32]),
         "silo_synth_owned_count": (u32, [vp]),
         "silo_synth_owned": (u32, [vp, u32]),
         "silo_synth_free": (None, [vp]),
@@ -170,9 +170,9 @@ class Database:
 
     @classmethod
     def synthetic(cls, n_sequences, seed, with_amino_acids=False, explicit_sequences=False, genome_length=0, n_threads=0,
-                  reference_genomes=None, world=1, rank=0):
+                  reference_genomes=None, world=1, rank=0, row_slices=1):
         ref = reference_genomes or ROOT / "tests" / "golden" / "exampleDataset1000Sequences" / "reference_genomes.json"
-        s = host().silo_synth_generate(str(ref).encode(), n_sequences, seed, int(with_amino_acids), int(explicit_sequences), genome_length, n_threads, world, rank)
+        s = host().silo_synth_generate(str(ref).encode(), n_sequences, seed, int(with_amino_acids), int(explicit_sequences), genome_length, n_threads, world, rank, row_slices)
         if not s:
             raise _error()
         db = cls(host().silo_synth_db(s), owner=s)
