@@ -281,6 +281,27 @@ char* silo_engine_execute_sharded(void* engine_, const char* query_json, int is_
    return out;
 }
 
+// Aggregated (with or without groupByFields) on a sharded database: every rank calls silo_engine_execute_partial, any channel
+// carries the texts to one rank (the harness uses torch.distributed.gather_object), silo_merge_partials adds equal tuples up and
+// applies orderByFields / limit / offset. `db` supplies the metadata configuration (any rank's Database has it).
+char* silo_engine_execute_partial(void* engine_, const char* query_json) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      out = capi::dupString(dumpJson(engine.executeAggregatedPartial(parseQuery(query_json))));
+   });
+   return out;
+}
+char* silo_merge_partials(const void* db_, const char* query_json, const char* const* partials, uint32_t n) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      const Query query = parseQuery(query_json);
+      std::vector<std::string> texts(partials, partials + n);
+      out = capi::dupString(dumpJson(engine::mergeAggregatedPartials(query.action, static_cast<const Database*>(db_)->config, texts)));
+   });
+   return out;
+}
+
 // Test hook for the host worker pool (tests/test_host_cpu.py; no device involved): runs n_jobs jobs that add
 // their index + 1 to a sum, `rounds` batches in a row, on `n_threads` workers + the caller; job `throw_at` (if >= 0)
 // throws. Returns the sum of the last batch, or -1 when the exception came back out of run().

@@ -380,10 +380,31 @@ class DeviceDatabase {
       std::vector<std::vector<uint32_t>>().swap(d->codes);
       return *(group_dictionaries_[meta.name] = std::move(d));
    }
+   // This process's share of an Aggregated query (with or without groupByFields): the entries for the partitions it owns, not
+   // ordered, not limited -- what mergeAggregatedPartials (host/group_by.hpp) adds up over the processes of a sharded database.
+   QueryResult executeAggregatedPartial(const Query& query) const {
+      const Action& action = query.action;
+      if (action.type != ActionType::AGGREGATED) throw QueryCompilationException("partial results exist for Aggregated actions (the Mutations tables of the ranks are summed on the devices)");
+      (void)parseGroupByFields(db.config, action.group_by_fields);
+      action.validateOrderByFields();
+      if (!action.group_by_fields.empty()) return executeGroupedUnordered(query);
+      CompiledFilter cf;
+      compileFilter(*query.filter, cf);
+      FusedResult fused;
+      runFused(cf, {}, 0, 0, fused);
+      QueryResultEntry entry;
+      entry.fields["count"] = static_cast<int32_t>(fused.count());
+      return QueryResult{{entry}};
+   }
    QueryResult executeGrouped(const Query& query) const {
       const Action& action = query.action;
-      const std::vector<ColumnMetadata> fields = parseGroupByFields(db.config, action.group_by_fields);   // validateOrderByFields starts with it (aggregated.cpp:71-73)
-      return action.executeAndOrder([&]() -> QueryResult {
+      (void)parseGroupByFields(db.config, action.group_by_fields);   // validateOrderByFields starts with it (aggregated.cpp:71-73)
+      return action.executeAndOrder([&]() -> QueryResult { return executeGroupedUnordered(query); });
+   }
+   QueryResult executeGroupedUnordered(const Query& query) const {
+      const Action& action = query.action;
+      const std::vector<ColumnMetadata> fields = parseGroupByFields(db.config, action.group_by_fields);
+      return [&]() -> QueryResult {
          if (owned.empty()) return {};
          CompiledFilter cf;
          compileFilter(*query.filter, cf);
@@ -401,7 +422,7 @@ class DeviceDatabase {
             rows.resize(n);
          }
          return groupedResult(dictionaries, rows.data(), n);
-      });
+      }();
    }
 
    // ---- one query = one submission (include/silo_b200.h: sb_query_mutations / sb_query_prepare) -----------------------

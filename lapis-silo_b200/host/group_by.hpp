@@ -139,4 +139,42 @@ inline QueryResult groupedResult(const std::vector<const GroupDictionary*>& dict
    return result;
 }
 
+// ---- Aggregated over a database whose partitions live in several processes (one per GPU) ------------------------------------
+// Every process answers for ITS partitions without ordering and limits (a partial: the entries of aggregated.cpp:46-56), one
+// process merges them the way aggregated.cpp:138-148 merges the partitions' maps -- equal tuples add up -- and then orders.
+inline FieldValue fieldFromJson(const json::Value& v) {
+   if (v.is_null()) return std::nullopt;
+   if (v.is_string()) return v.s;
+   if (v.is_number_float()) return v.d;
+   return static_cast<int32_t>(v.is_number_unsigned() ? static_cast<int64_t>(v.u) : v.i);
+}
+inline QueryResult mergeAggregatedPartials(const Action& action, const DatabaseConfig& config, const std::vector<std::string>& partial_responses) {
+   if (action.type != ActionType::AGGREGATED) throw QueryCompilationException("only Aggregated results are merged on the host (Mutations tables are summed on the devices)");
+   (void)parseGroupByFields(config, action.group_by_fields);
+   return action.executeAndOrder([&]() -> QueryResult {
+      std::map<std::map<std::string, FieldValue>, uint32_t> merged;      // tuple -> count (uint32 like the reference's map values)
+      for (const std::string& text : partial_responses) {
+         const json::Value j = json::parse(text);
+         for (const auto& entry : j["queryResult"].arr) {
+            std::map<std::string, FieldValue> tuple;
+            uint32_t count = 0;
+            for (const auto& [name, value] : entry.obj) {
+               if (name == "count") count = static_cast<uint32_t>(value.is_number_unsigned() ? value.u : static_cast<uint64_t>(value.i));
+               else tuple[name] = fieldFromJson(value);
+            }
+            merged[tuple] += count;
+         }
+      }
+      QueryResult result;
+      if (action.group_by_fields.empty() && merged.empty()) merged[{}] = 0;      // aggregateWithoutGrouping always yields one row
+      for (auto& [tuple, count] : merged) {
+         QueryResultEntry e;
+         e.fields = tuple;
+         e.fields["count"] = static_cast<int32_t>(count);
+         result.query_result.push_back(std::move(e));
+      }
+      return result;
+   });
+}
+
 }  // namespace silo::engine

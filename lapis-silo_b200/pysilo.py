@@ -75,6 +75,8 @@ def host():
         "silo_prepared_elapsed_ms": (ctypes.c_float, [vp]),
         "silo_engine_set_plan_cache": (None, [vp, ctypes.c_int]),
         "silo_engine_execute_sharded": (vp, [vp, cp, ctypes.c_int]),
+        "silo_engine_execute_partial": (vp, [vp, cp]),
+        "silo_merge_partials": (vp, [vp, cp, ctypes.POINTER(cp), u32]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32, u32]),
         "silo_synth_owned_count": (u32, [vp]),
         "silo_synth_owned": (u32, [vp, u32]),
@@ -322,6 +324,11 @@ class Engine:
         """multi-GPU: every rank calls with the same text in the same order; rank 0 gets the response text"""
         return _take_string(host().silo_engine_execute_sharded(self.handle, query_json.encode() if isinstance(query_json, str) else query_json, int(is_root)))
 
+    def execute_partial(self, query):
+        """Aggregated (with or without groupByFields) on a sharded database: this rank's entries, unordered (see merge_partials)"""
+        q = query if isinstance(query, str) else json.dumps(query)
+        return _take_string(host().silo_engine_execute_partial(self.handle, q.encode()))
+
     def mutation_counts(self, query, sequence_name, table_len):
         q = query if isinstance(query, str) else json.dumps(query)
         out = np.zeros(table_len, dtype=np.uint32)
@@ -484,6 +491,13 @@ class Prepared:
         if self.handle:
             host().silo_prepared_free(self.handle)
             self.handle = None
+
+
+def merge_partials(db, query, partial_texts):
+    """one rank: the response of an Aggregated query from the ranks' Engine.execute_partial texts (equal tuples add up, then order / limit)"""
+    q = query if isinstance(query, str) else json.dumps(query)
+    arr = (ctypes.c_char_p * max(len(partial_texts), 1))(*[t.encode() for t in partial_texts])
+    return json.loads(_take_string(host().silo_merge_partials(db.handle, q.encode(), arr, len(partial_texts))))["queryResult"]
 
 
 def rows_from_table(db, query, sequence_name, counts):

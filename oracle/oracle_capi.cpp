@@ -46,6 +46,17 @@ char* oracle_execute_query(const void* db, const char* query_json, int faithful,
 }
 
 // Bounded sample for the timed CPU baseline: the query restricted to `partitions`; returns seconds of
+// the query restricted to some partitions (the others count as empty filters): what one rank of a sharded database answers
+char* oracle_execute_query_subset(const void* db, const char* query_json, const uint32_t* partitions, uint32_t n) {
+   char* out = nullptr;
+   guarded([&] {
+      oracle::Options options{false, 0, std::vector<uint32_t>(partitions, partitions + n)};
+      auto result = oracle::executeQuery(*static_cast<const silo::Database*>(db), query_json, options);
+      out = dupString(silo::dumpJson(result));
+   });
+   return out;
+}
+
 // wall-clock spent in executeQuery (filter + action), or a negative value on error.
 double oracle_time_query_subset(const void* db, const char* query_json, int faithful, int threads, const uint32_t* partitions, uint32_t n, uint64_t* result_rows) {
    double seconds = -1;

@@ -61,6 +61,22 @@ def execute(db, query, faithful=True, threads=0):
         lib().oracle_free(r)
 
 
+def execute_subset_text(db, query, partitions):
+    """response text of `query` restricted to `partitions` (what one rank of a sharded database answers)"""
+    q = query if isinstance(query, str) else json.dumps(query)
+    arr = (ctypes.c_uint32 * max(len(partitions), 1))(*partitions)
+    fn = lib().oracle_execute_query_subset
+    fn.restype = ctypes.c_void_p
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32]
+    r = fn(db.handle, q.encode(), arr, len(partitions))
+    if not r:
+        raise _err()
+    try:
+        return ctypes.string_at(r).decode()
+    finally:
+        lib().oracle_free(r)
+
+
 def eval_optree(tree):
     ptr, n = ctypes.c_void_p(), ctypes.c_size_t()
     if lib().oracle_eval_optree(json.dumps(tree).encode(), ctypes.byref(ptr), ctypes.byref(n)) != 0:

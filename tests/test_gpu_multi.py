@@ -31,6 +31,13 @@ def _queries(db):
     return out
 
 
+def _aggregated_queries(db):
+    flt = _queries(db)[0]["filterExpression"]
+    return [{"action": {"type": "Aggregated"}, "filterExpression": flt},
+            {"action": {"type": "Aggregated", "groupByFields": ["region", "pangoLineage"], "orderByFields": ["pangoLineage", "region"]}, "filterExpression": flt},
+            {"action": {"type": "Aggregated", "groupByFields": ["age", "date"], "orderByFields": [{"field": "count", "order": "descending"}, "age", "date"], "limit": 20}, "filterExpression": {"type": "True"}}]
+
+
 def _worker(rank, port, out_dir):
     sys.path.insert(0, str(ROOT / "lapis-silo_b200"))
     sys.path.insert(0, str(ROOT / "tests"))
@@ -80,8 +87,15 @@ def _worker(rank, port, out_dir):
         t.join()
     torch.cuda.synchronize()
     dist.barrier()
+    # Aggregated (count and groupByFields): every rank's partial answer travels to rank 0, which merges (host/group_by.hpp)
+    aggregated = []
+    for q in _aggregated_queries(db):
+        gathered = [None] * WORLD if rank == 0 else None
+        dist.gather_object(engine.execute_partial(q), gathered, dst=0)
+        if rank == 0:
+            aggregated.append(pysilo.merge_partials(db, q, gathered))
     if rank == 0:
-        Path(out_dir, "rank0.json").write_text(json.dumps({"sequential": sequential, "prepared": prepared, "threaded": results, "schedule": schedule}))
+        Path(out_dir, "rank0.json").write_text(json.dumps({"sequential": sequential, "prepared": prepared, "threaded": results, "schedule": schedule, "aggregated": aggregated}))
     pysilo.comm_free(engine)
     engine.close()
     dist.barrier()
@@ -105,4 +119,5 @@ def test_sharded_queries_equal_the_whole_database_oracle(libs, tmp_path):
     assert [json.loads(t) for t in got["sequential"]] == expect + expect
     assert [json.loads(t) for t in got["prepared"]] == expect[:2]
     assert [json.loads(t) for t in got["threaded"]] == [expect[q] for _, q in got["schedule"]]
+    assert got["aggregated"] == [oracle.execute(whole, q) for q in _aggregated_queries(whole)]
     assert len(expect[0]["queryResult"]) > 0 and len(expect[4]["queryResult"]) > 0 and expect[5]["queryResult"] == []

@@ -89,3 +89,22 @@ def test_worker_pool_runs_every_job_and_propagates_errors(libs):
         assert h.silo_test_worker_pool(threads, jobs, rounds, -1) == jobs * (jobs + 1) // 2
     assert h.silo_test_worker_pool(6, 23, 1, 7) == -1        # an exception inside a job comes back to the caller
     assert h.silo_test_worker_pool(6, 23, 3, -1) == 276      # and the pool is usable again afterwards (a fresh pool here)
+
+
+def test_aggregated_partials_of_a_sharded_database_merge_to_the_whole(libs, synth_small):
+    """host/group_by.hpp mergeAggregatedPartials (what rank 0 of a sharded database does): the unordered answers for two disjoint
+    sets of partitions -- here from the oracle -- add up to the oracle's answer over all partitions, with ordering and limits"""
+    import copy
+    pysilo, oracle = libs
+    clade = synth_small.clade_mutations()
+    flt = {"type": "N-Of", "numberOfMatchers": 1, "matchExactly": False, "children": [{"type": "NucleotideEquals", "position": p + 1, "symbol": s} for p, s in clade[:5]]}
+    parts = list(range(synth_small.n_partitions))
+    shards = [parts[0::2], parts[1::2]]
+    for action in [{"type": "Aggregated"}, {"type": "Aggregated", "groupByFields": ["region"], "orderByFields": ["region"]},
+                   {"type": "Aggregated", "groupByFields": ["age", "pangoLineage", "qc", "date"], "orderByFields": [{"field": "count", "order": "descending"}, "pangoLineage", "age", "qc", "date"], "limit": 9, "offset": 2}]:
+        query = {"action": action, "filterExpression": flt}
+        partial = copy.deepcopy(query)
+        for key in ("orderByFields", "limit", "offset"):
+            partial["action"].pop(key, None)
+        texts = [oracle.execute_subset_text(synth_small, partial, shard) for shard in shards]
+        assert pysilo.merge_partials(synth_small, query, texts) == oracle.execute(synth_small, query)

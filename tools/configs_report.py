@@ -97,7 +97,7 @@ def main():
         engine = pysilo.Engine(db, 0)
         for label, f in (("C4 (HasAminoAcidMutation S:501)", {"type": "HasAminoAcidMutation", "sequenceName": "S", "position": 501}),
                          ("C4 (HasNucleotideMutation 23063)", {"type": "HasNucleotideMutation", "position": 23063})):
-            measure(pysilo, torch, engine, db, label, {"action": {"type": "AminoAcidMutations", "minProportion": 0.05}, "filterExpression": f}, args.c4_rows)
+            measure(pysilo, torch, engine, db, label, {"action": {"type": "AminoAcidMutations", "minProportion": 0.05}, "filterExpression": f}, args.c4_rows, (0, 0))
         engine.close()
     if "C5" in only:       # 40 M sequences: Mutations under a top-level clade with sublineages, and under True
         db = pysilo.Database.synthetic(args.c5_rows, 0x51100005)
