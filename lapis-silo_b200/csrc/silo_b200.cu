@@ -61,9 +61,33 @@ struct Slab {
 // Everything one query in flight needs besides the index: the lowered plans, the filter results, the scratch of the row-wise
 // leaves, the per-sequence action state, the count tables, the selected rows, and the pinned images the copies go through.
 // A lane owns one (one-shot queries); a prepared query owns its own (fixed addresses: its launches are a CUDA graph).
+// A query over several sequences (AminoAcidMutations over all genes: twelve count tables) runs the sequences' count kernels side
+// by side: sequence k goes to branch k mod n -- a stream pair of its own that forks from the query's stream after the
+// classification and joins it before the query ends (parallel branches of the CUDA graph for a prepared query).
+struct SeqBranch {
+   cudaStream_t main = nullptr, side = nullptr;
+   cudaEvent_t fork2 = nullptr, join2 = nullptr, done = nullptr;
+};
+constexpr size_t SEQ_BRANCHES = 4;
 struct QueryBuffers {
    GrowDevice blob, results, scratch, locs, deep_stack, action, tables, rows;
    PinnedBuffer staging, out_host;
+   std::vector<SeqBranch> branches;
+   cudaEvent_t ev_branches = nullptr;
+   void ensureBranches(size_t n) {      // never inside a stream capture
+      if (!ev_branches) SB_CUDA(cudaEventCreateWithFlags(&ev_branches, cudaEventDisableTiming));
+      while (branches.size() < std::min(n, SEQ_BRANCHES)) {
+         SeqBranch b;
+         SB_CUDA(cudaStreamCreateWithFlags(&b.main, cudaStreamNonBlocking));
+         SB_CUDA(cudaStreamCreateWithFlags(&b.side, cudaStreamNonBlocking));
+         for (cudaEvent_t* e : {&b.fork2, &b.join2, &b.done}) SB_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+         branches.push_back(b);
+      }
+   }
+   ~QueryBuffers() {
+      for (auto& b : branches) { cudaEventDestroy(b.fork2); cudaEventDestroy(b.join2); cudaEventDestroy(b.done); cudaStreamDestroy(b.side); cudaStreamDestroy(b.main); }
+      if (ev_branches) cudaEventDestroy(ev_branches);
+   }
 };
 
 }  // namespace sb

@@ -1,4 +1,4 @@
-"""Two GPUs, one process each (NCCL): a database sharded by DatabasePartition, the count tables summed inside the query's
+"""Two GPUs, one process each (NCCL): a database sharded by DatabasePartition (row slices of every lineage partition), the count tables summed inside the query's
 submission (sb_comm_init -> ncclReduce to rank 0), against the oracle over the WHOLE database in one process.
 Also two host threads per rank issuing queries in an order both ranks agree on (collective calls: include/silo_b200.h).
 Skipped with fewer than two devices."""
@@ -49,7 +49,8 @@ def _worker(rank, port, out_dir):
     torch.cuda.set_device(rank)
     device = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=WORLD, device_id=device)
-    db = pysilo.Database.synthetic(N_ROWS, SEED, genome_length=GENOME, world=WORLD, rank=rank)
+    # every lineage partition cut into WORLD row slices, one per rank (bench.py --shard rows); the oracle below sees whole partitions
+    db = pysilo.Database.synthetic(N_ROWS, SEED, genome_length=GENOME, world=WORLD, rank=rank, row_slices=WORLD)
     engine = pysilo.Engine(db, rank, db.owned)
     id_t = torch.zeros(128, dtype=torch.uint8, device=device)
     if rank == 0:
