@@ -167,6 +167,8 @@ struct SeqDev {
    const uint4* miss_inline;         // [2 per row]
    const uint64_t* miss_inline_base; // [P] index of the partition's first row
    uint32_t miss_narrow, pad_inline;
+   const uint32_t* miss_any;         // per partition one bit per row: the row misses at least one position (a short gene: a few percent of the rows)
+   const uint64_t* miss_any_base;    // [P] word offset of the partition's bits
    const uint32_t* miss_tile_bits;   // per partition [n_tiles][ceil(n_rows / 32)]: bit = the row misses some position of the tile
    const uint64_t* miss_tile_base;   // [P] word offset of the partition's block
    const uint32_t* part_rows;        // [P] sequence_count of the partition's store, 0 = the partition has no store of this sequence

@@ -433,6 +433,7 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
    const uint32_t word_begin = row0 >> 5, word_end = (row1 + 31) >> 5;
    int at_window_start = 0;      // intervals that begin at the window's first position (leading runs: nearly every row) are counted in a register
    const uint4* records = s.miss_inline + s.miss_inline_base[partition] * 2;
+   const uint32_t* any_missing = s.miss_any + s.miss_any_base[partition];
    auto apply = [&](uint32_t start, uint32_t end) {      // an empty slot is (0, 0): nothing happens
       const uint32_t lo = max(start, w0), hi = min(end, w1);
       if (lo < hi) {
@@ -441,7 +442,7 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
       }
    };
    for (uint32_t word = word_begin + threadIdx.x; word < word_end; word += K2_THREADS) {
-      uint32_t bits = __ldg(q.filter32 + word);
+      uint32_t bits = __ldg(q.filter32 + word) & __ldg(any_missing + word);      // filtered rows that miss anything at all (a short gene: few)
       if ((word + 1) * 32 > row1) bits &= ~0u >> (32 - (row1 & 31));      // row1 is the partition's end here: row blocks are multiples of 32 rows
       if (bits) any_row = true;
       while (bits) {

@@ -134,7 +134,8 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<int8_t> deleted, flipped;
    DeviceBuffer<uint32_t> miss_row_off;
    DeviceBuffer<uint2> miss_iv;
-   DeviceBuffer<uint64_t> miss_row_base, miss_iv_base, miss_tile_base, miss_inline_base;
+   DeviceBuffer<uint64_t> miss_row_base, miss_iv_base, miss_tile_base, miss_inline_base, miss_any_base;
+   DeviceBuffer<uint32_t> miss_any;
    DeviceBuffer<uint4> miss_inline;
    DeviceBuffer<uint32_t> miss_tile_bits;
    DeviceBuffer<uint32_t> full_tables;   // [P][sigma * length]
@@ -324,17 +325,22 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    std::vector<uint2> iv;
    std::vector<uint64_t> row_base(n_partitions, 0), iv_base(n_partitions, 0), inline_base(n_partitions, 0);
    std::vector<uint32_t> inline_words;      // 8 per row
+   std::vector<uint32_t> any_words;         // 1 bit per row
+   std::vector<uint64_t> any_base(n_partitions, 0);
    const bool narrow = L <= 65535;
    for (uint32_t p = 0; p < n_partitions; ++p) {
       row_base[p] = row_off.size();
       iv_base[p] = iv.size();
       inline_base[p] = inline_words.size() / 8;
+      any_base[p] = any_words.size();
       if (seq.store_of_partition[p] < 0) { row_off.push_back(0); continue; }
       HostStore& st = *stores[seq.store_of_partition[p]];
       inline_words.resize(inline_words.size() + size_t(st.n_rows) * 8, 0u);
+      any_words.resize(any_words.size() + (size_t(st.n_rows) + 31) / 32 + 1, 0u);
       for (uint32_t row = 0; row < st.n_rows; ++row) {
          uint32_t* rec = inline_words.data() + (inline_base[p] + row) * 8;
          const uint32_t b = st.miss_row_off[row], e = st.miss_row_off[row + 1];
+         if (e > b) any_words[any_base[p] + row / 32] |= 1u << (row & 31);
          if (e - b > (narrow ? 8u : 4u)) { for (int k = 0; k < 8; ++k) rec[k] = 0xFFFFFFFFu; continue; }
          for (uint32_t j = b; j < e; ++j) {
             if (narrow) rec[j - b] = st.miss_iv[j].x | (st.miss_iv[j].y << 16);
@@ -377,7 +383,9 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    seq.miss_inline_base.upload(inline_base);
    seq.miss_inline.alloc(inline_words.size() / 4);
    if (!inline_words.empty()) SB_CUDA(cudaMemcpy(seq.miss_inline.ptr, inline_words.data(), inline_words.size() * 4, cudaMemcpyHostToDevice));
-   stats.missing_bytes += seq.miss_inline.bytes();
+   seq.miss_any_base.upload(any_base);
+   seq.miss_any.upload(any_words);
+   stats.missing_bytes += seq.miss_inline.bytes() + seq.miss_any.bytes();
    std::vector<uint32_t>().swap(inline_words);
    {  // coarse index of the missing-symbol intervals: per (partition, tile) the rows that miss some position of the tile.
       // BitmapSelection(position) then searches the intervals of those rows only (a few percent of the partition).
@@ -411,6 +419,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    d.miss_row_off = seq.miss_row_off.ptr; d.miss_iv = seq.miss_iv.ptr; d.miss_row_base = seq.miss_row_base.ptr; d.miss_iv_base = seq.miss_iv_base.ptr;
    d.miss_tile_bits = seq.miss_tile_bits.ptr; d.miss_tile_base = seq.miss_tile_base.ptr;
    d.miss_inline = seq.miss_inline.ptr; d.miss_inline_base = seq.miss_inline_base.ptr; d.miss_narrow = narrow ? 1u : 0u;
+   d.miss_any = seq.miss_any.ptr; d.miss_any_base = seq.miss_any_base.ptr;
    d.part_rows = seq.part_rows.ptr; d.runs = seq.runs.ptr; d.n_runs = seq.n_runs;
    d.length = L; d.sigma = sigma; d.tile_positions = tp; d.n_tiles = seq.n_tiles; d.n_partitions = n_partitions;
    d.n_items = seq.n_items; d.n_slabs = n_slabs;

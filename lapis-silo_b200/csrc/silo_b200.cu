@@ -214,11 +214,22 @@ inline std::unique_lock<std::mutex> collectiveLock(sb_db* db) {      // held onl
    return lock;
 }
 inline void useDevice(const sb_db* db) { SB_CUDA(cudaSetDevice(db->device)); }
-// the lane of the calling thread (threads are numbered in the order in which they first call in)
-inline sb_lane* laneOf(sb_db* db) {
+// A lane for the calling thread, locked: the thread's home lane (threads are numbered in the order in which they first call in)
+// if it is free, else the next free one -- a ninth request thread does not queue behind the first while other lanes idle.
+struct LaneHold { sb_lane* lane; std::unique_lock<std::mutex> lock; };
+inline sb_lane*& lastLaneOfThread() { thread_local sb_lane* last = nullptr; return last; }
+inline LaneHold holdLane(sb_db* db) {
    static std::atomic<uint32_t> next_thread{0};
    thread_local uint32_t my_index = next_thread.fetch_add(1);
-   return db->lanes[my_index % db->lanes.size()].get();
+   const size_t n = db->lanes.size();
+   for (size_t k = 0; k < n; ++k) {
+      sb_lane* ln = db->lanes[(my_index + k) % n].get();
+      std::unique_lock<std::mutex> lock(ln->mutex, std::try_to_lock);
+      if (lock.owns_lock()) { lastLaneOfThread() = ln; return {ln, std::move(lock)}; }
+   }
+   sb_lane* ln = db->lanes[my_index % n].get();
+   lastLaneOfThread() = ln;
+   return {ln, std::unique_lock<std::mutex>(ln->mutex)};
 }
 }
 
@@ -470,8 +481,8 @@ extern "C" int sb_mutation_rows_from_table_static(sb_db* db, const char* store_n
    return guarded([&] {
       SB_REQUIRE(db && db->finalized, "sb_mutation_rows_from_table_static before sb_db_finalize");
       SB_REQUIRE(device_counts && n_rows && (rows || capacity == 0), "null argument");
-      sb_lane* ln = laneOf(db);
-      std::lock_guard<std::mutex> lock(ln->mutex);
+      const LaneHold hold = holdLane(db);
+      sb_lane* ln = hold.lane;
       useDevice(db);
       Sequence& seq = findSequence(db, store_name);
       const RowSelection rs = makeRowSelection(seq, min_proportion, valid, n_valid);
