@@ -42,9 +42,11 @@ def measure(pysilo, torch, engine, db, name, query, rows, device_table=None, cal
         for _ in range(3):
             prepared.run_device()
         samples = []
+        torch.cuda.profiler.start()      # `ncu --profile-from-start off` sees the replays only
         for _ in range(calls):
             prepared.run_device()
             samples.append(prepared.elapsed_ms())
+        torch.cuda.profiler.stop()
         ms = statistics.median(samples)
         info = prepared.algorithmic_bytes(device_table[0])
         line.update({"device_ms_per_query": ms, "device_queries_per_s": 1e3 / ms, "algorithmic_bytes": info["alg_bytes"], "k1_algorithmic_bytes": info["k1_bytes"],
