@@ -60,7 +60,7 @@ int guarded(F&& f) {
 // Rows of a partition are cut into SLABS of 4 container keys (262,144 rows, a 32 KB slice of the dense
 // filter bitset that the scan keeps in shared memory). The stored roaring containers of a sequence are
 // grouped by (position tile, slab) SEGMENTS. Inside a segment
-//   * containers (array or run) of cardinality <= FLAT_MAX -- 99.9 % of them in real data: a handful of
+//   * containers (array or run) of cardinality <= FLAT_MAX -- 99.9 % of them hold at most 16 values in real data: a handful of
 //     rows carrying a private mutation -- are flattened into 4-byte POSTINGS
 //         slot':14 << 18 | row_in_slab:18          slot' = symbol * tile_positions + position_in_tile
 //     sorted ascending; the scan streams them with 128-bit loads, one probe of the shared-memory filter each;
@@ -73,7 +73,7 @@ constexpr uint32_t TILE_POSITIONS = 256;     // positions per tile (shared-memor
 constexpr uint32_t MAX_TILE_POSITIONS = 512;
 constexpr uint32_t SLAB_KEYS = 4;            // container keys per slab
 constexpr uint32_t SLAB_WORDS32 = SLAB_KEYS * 2048;   // 32-bit filter words per slab (32 KB)
-constexpr uint32_t FLAT_MAX = 16;            // containers up to this cardinality become postings
+constexpr uint32_t FLAT_MAX = 64;            // containers up to this cardinality become postings (pool.cuh flatMax)
 constexpr uint32_t POSTING_ROW_BITS = 18;
 constexpr uint32_t POSTING_ROW_MASK = (1u << POSTING_ROW_BITS) - 1u;
 

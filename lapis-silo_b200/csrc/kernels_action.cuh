@@ -234,6 +234,28 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
       const bool new_slab = item.slab != cur_slab;        // the items of a run keep the filter slice
       cur_slab = item.slab;
       uint32_t* next_unit = unit_counters + turn;
+      // Work units of the item, handed out to the warps through a shared counter (a warp that is busy with a bitset
+      // simply takes fewer): first the large containers -- a bitset as two halves of 4 KB, anything else whole --
+      // then the postings in chunks of 128 x 16 bytes. The first unit of a warp is its warp id; the loads of a posting
+      // chunk are issued one unit ahead (and before waiting for the filter: they do not depend on it).
+      const uint4* post4 = reinterpret_cast<const uint4*>(s.postings + item.post_begin);
+      const uint32_t n4 = (item.post_end - item.post_begin + 3u) >> 2;
+      const uint32_t n_large_units = 2u * (item.large_end - item.large_begin);
+      const uint32_t n_units = n_large_units + (n4 + CHUNK4 - 1) / CHUNK4;
+      uint4 v[K1_UNROLL];
+      auto loadChunk = [&](uint32_t unit, uint4 (&dst)[K1_UNROLL]) {
+         if (unit < n_large_units || unit >= n_units) return;
+         const uint32_t base = (unit - n_large_units) * CHUNK4 + lane;
+#pragma unroll
+         for (int k = 0; k < K1_UNROLL; ++k) dst[k] = base + k * 32 < n4 ? loadStream(post4 + base + k * 32) : none;
+      };
+      auto grab = [&]() {
+         uint32_t next = 0;
+         if (lane == 0) next = atomicAdd(next_unit, 1u);
+         return __shfl_sync(0xFFFFFFFFu, next, 0);
+      };
+      uint32_t unit = warp;
+      loadChunk(unit, v);      // issued before the barrier: the loads travel while the other warps finish the previous item's flush
       __syncthreads();                                    // the previous flush (and its zeroing) is done; nobody reads the other item slot any more
       if (threadIdx.x == 0) {
          if (new_slab) {
@@ -256,28 +278,6 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
             flush_flip[f] = s.flipped[size_t(item.partition) * s.length + pos];
          }
       }
-      // Work units of the item, handed out to the warps through a shared counter (a warp that is busy with a bitset
-      // simply takes fewer): first the large containers -- a bitset as two halves of 4 KB, anything else whole --
-      // then the postings in chunks of 128 x 16 bytes. The first unit of a warp is its warp id; the loads of a posting
-      // chunk are issued one unit ahead (and before waiting for the filter: they do not depend on it).
-      const uint4* post4 = reinterpret_cast<const uint4*>(s.postings + item.post_begin);
-      const uint32_t n4 = (item.post_end - item.post_begin + 3u) >> 2;
-      const uint32_t n_large_units = 2u * (item.large_end - item.large_begin);
-      const uint32_t n_units = n_large_units + (n4 + CHUNK4 - 1) / CHUNK4;
-      uint4 v[K1_UNROLL];
-      auto loadChunk = [&](uint32_t unit, uint4 (&dst)[K1_UNROLL]) {
-         if (unit < n_large_units || unit >= n_units) return;
-         const uint32_t base = (unit - n_large_units) * CHUNK4 + lane;
-#pragma unroll
-         for (int k = 0; k < K1_UNROLL; ++k) dst[k] = base + k * 32 < n4 ? loadStream(post4 + base + k * 32) : none;
-      };
-      auto grab = [&]() {
-         uint32_t next = 0;
-         if (lane == 0) next = atomicAdd(next_unit, 1u);
-         return __shfl_sync(0xFFFFFFFFu, next, 0);
-      };
-      uint32_t unit = warp;
-      loadChunk(unit, v);
       if (new_slab) { mbarWait(bar, parity); }
       // thread 0 fetches the CTA's next item while the other warps stream
       if (threadIdx.x == 0) fetchNext(item_slots + (turn ^ 1u));
@@ -504,21 +504,32 @@ k2_missing(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, ui
    const uint32_t n_filtered = q.cardinality;
    const int8_t* deleted = s.deleted + size_t(partition) * s.length;
    const int8_t* flipped = s.flipped + size_t(partition) * s.length;
-   for (uint32_t i = threadIdx.x; i < width; i += blockDim.x) {
-      const uint32_t pos = w0 + i;
-      const uint32_t miss = uint32_t(diff[i]);
-      if (miss == 0 && !first_block) continue;
-      const int d = deleted[pos];
-      uint32_t add = 0u - miss;
-      if (first_block) {
-         const int f = flipped[pos];
-         add += n_filtered;
-         if (f >= 0) {
-            if (!full_mode) add -= n_filtered;               // the flipped symbol's |F| part of the deleted symbol's count
-            atomicAdd(counts + size_t(f) * s.length + pos, n_filtered);
-         }
+   // four positions per thread at a time: their flag loads are issued together (one round trip instead of four in a row)
+   for (uint32_t i0 = threadIdx.x; i0 < width; i0 += 4 * blockDim.x) {
+      int d[4], f[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+         const uint32_t i = i0 + k * blockDim.x;
+         d[k] = f[k] = -1;
+         if (i < width && (first_block || diff[i] != 0)) { d[k] = deleted[w0 + i]; if (first_block) f[k] = flipped[w0 + i]; }
       }
-      if (d >= 0 && add) atomicAdd(counts + size_t(d) * s.length + pos, add);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+         const uint32_t i = i0 + k * blockDim.x;
+         if (i >= width) continue;
+         const uint32_t pos = w0 + i;
+         const uint32_t miss = uint32_t(diff[i]);
+         if (miss == 0 && !first_block) continue;
+         uint32_t add = 0u - miss;
+         if (first_block) {
+            add += n_filtered;
+            if (f[k] >= 0) {
+               if (!full_mode) add -= n_filtered;               // the flipped symbol's |F| part of the deleted symbol's count
+               atomicAdd(counts + size_t(f[k]) * s.length + pos, n_filtered);
+            }
+         }
+         if (d[k] >= 0 && add) atomicAdd(counts + size_t(d[k]) * s.length + pos, add);
+      }
    }
 }
 

@@ -85,7 +85,7 @@ __global__ void locate_leaves(const SeqDev* __restrict__ seqs, const LocJob* __r
          const bool below = lo + lane < hi && __ldg(s.postings + lo + lane) < target;
          lo += __popc(__ballot_sync(0xFFFFFFFFu, below));
       }
-      // a slot holds at most SLAB_KEYS containers of at most FLAT_MAX postings in a slab
+      // the postings of the slot in this slab (at most SLAB_KEYS small containers)
       uint32_t n = 0;
       for (uint32_t base = lo; base < next.post_start; base += 32) {
          const bool same = base + lane < next.post_start && (__ldg(s.postings + base + lane) >> POSTING_ROW_BITS) == job.slot2;

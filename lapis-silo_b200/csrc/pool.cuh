@@ -159,11 +159,24 @@ inline uint64_t itemWeightCap() {   // bytes of postings + large payload per Mut
 
 // bytes of postings + large payload per RUN of work items (one slab, consecutive tiles): what a CTA of the scan takes at a time.
 // Large enough to pay for the 32 KB filter copy, small enough that every resident CTA gets several (SB_RUN_CAP_KB: tuning).
+// Items per run: a CTA walks the items of its run one after the other (each costs a few dependent memory round trips whatever it
+// holds), so runs of many tiny items serialise a small database on a handful of CTAs -- the 1,000-sequence dataset (1,170 items)
+// took 148 us in 20 runs of up to 64 items. Two items per run keep half of the filter copies away and every CTA busy.
+constexpr uint32_t RUN_MAX_ITEMS = 2;
 inline uint64_t runWeightCap(uint64_t total_weight) {
    const char* e = getenv("SB_RUN_CAP_KB");
    if (e && atoi(e) > 0) return uint64_t(atoi(e)) * 1024;
    (void)total_weight;
    return 96 * 1024;      // measured at 40 M rows: 1 item per run, 96 KB and 256 KB runs take 0.177 / 0.177 / 0.195 ms (long runs cost balance at the end of the scan)
+}
+
+// Containers up to this cardinality become postings (SB_FLAT_MAX: tuning). A container that stays in the large pool costs a warp
+// two dependent memory round trips (directory entry, payload) whatever it holds: a one-tile gene of the amino-acid stores packs
+// hundreds of 20-60-value arrays into one work item, which then took 200-380 us at 10 M rows.
+inline uint32_t flatMax() {
+   const char* e = getenv("SB_FLAT_MAX");
+   const uint32_t v = e && atoi(e) > 0 ? uint32_t(atoi(e)) : FLAT_MAX;
+   return std::min<uint32_t>(v, 1024u);
 }
 
 inline uint32_t arraySplit() {   // values per large-array entry (SB_ARRAY_SPLIT: tuning; a multiple of 8 keeps the pieces 16-byte aligned)
@@ -213,6 +226,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
    const uint32_t filler = slots_per_tile << POSTING_ROW_BITS;
    const uint64_t item_cap = itemWeightCap();
    const uint32_t array_split = arraySplit();
+   const uint32_t flat_max = flatMax();
    for (uint32_t tile = 0; tile < seq.n_tiles; ++tile) {
       const uint32_t slot_end = (tile + 1) * slots_per_tile;
       for (uint32_t slab_id = 0; slab_id < n_slabs; ++slab_id) {
@@ -248,9 +262,9 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
             else if (c.kind == KIND_ARRAY) { stats.array_containers++; stats.array_values += c.size; }
             else { stats.run_containers++; stats.run_count += c.size; stats.run_values += cardinality; }
             const uint32_t head = (pk.slot2 << POSTING_ROW_BITS) | (key_local << 16);
-            if (c.kind == KIND_ARRAY && cardinality <= FLAT_MAX) {
+            if (c.kind == KIND_ARRAY && cardinality <= flat_max) {
                for (uint32_t i = 0; i < c.size; ++i) postings.push_back(head | src[i]);
-            } else if (c.kind == KIND_RUN && cardinality <= FLAT_MAX) {
+            } else if (c.kind == KIND_RUN && cardinality <= flat_max) {
                for (uint32_t r = 0; r < c.size; ++r) for (uint32_t v = src[2 * r], last = uint32_t(src[2 * r]) + src[2 * r + 1]; v <= last; ++v) postings.push_back(head | v);
             } else {
                // a big array container becomes several entries of at most `array_split` values: an entry is one warp's unit of
@@ -299,7 +313,7 @@ inline void packSequence(Sequence& seq, std::vector<std::unique_ptr<HostStore>>&
       const uint64_t run_cap = runWeightCap(total_weight);
       std::vector<uint64_t> run_weight;
       for (uint32_t k = 0; k < items.size(); ++k) {
-         const bool extend = !runs.empty() && items[runs.back().first_item].slab == items[k].slab && run_weight.back() + item_weight[k] <= run_cap && runs.back().n_items < 64;
+         const bool extend = !runs.empty() && items[runs.back().first_item].slab == items[k].slab && run_weight.back() + item_weight[k] <= run_cap && runs.back().n_items < RUN_MAX_ITEMS;
          if (extend) { runs.back().n_items++; run_weight.back() += item_weight[k]; }
          else { runs.push_back({k, 1, items[k].partition, 0}); run_weight.push_back(item_weight[k]); }
       }
