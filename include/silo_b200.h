@@ -204,6 +204,9 @@ int sb_query_prepare(sb_db* db, uint32_t n, const uint32_t* partitions, const sb
                      uint32_t n_sequences, const char* const* sequence_names, double min_proportion, const uint8_t* valid, uint32_t n_valid,
                      int use_graph, sb_query** out);
 int sb_query_run(sb_query* q, sb_sequence_rows* out, uint64_t* cardinalities);
+/* A batch of prepared queries from one host thread (SURVEY 8f "batched filter evaluation"): every query is enqueued on its own
+ * stream before the first is waited for. outs[i] (and cardinalities[i], may be null) belong to queries[i]; a query appears once. */
+int sb_query_run_many(sb_query* const* queries, uint32_t n, sb_sequence_rows* const* outs, uint64_t* const* cardinalities);
 /* the uint32[n_symbols][length] table of sequence `index` of the last run, in device memory (valid until the next run) */
 int sb_query_table_device(sb_query* q, uint32_t index, const void** device_counts, size_t* counts_len);
 /* CUDA-event time of the last sb_query_run, recorded on the query's own stream: first kernel to last copy */

@@ -212,6 +212,19 @@ int silo_prepared_run_device(void* engine_, void* prepared_, uint64_t* result_ro
       }
    });
 }
+// A batch of prepared queries from the calling thread (sb_query_run_many): texts[i] receives the response of prepared[i]
+// (free each with silo_free). Returns 0 on success.
+int silo_prepared_run_many(void* engine_, void* const* prepared, uint32_t n, char** texts) {
+   return capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      std::vector<DeviceDatabase::PreparedQuery*> queries;
+      std::vector<std::unique_lock<std::mutex>> locks;
+      for (uint32_t i = 0; i < n; ++i) { queries.push_back(static_cast<DeviceDatabase::PreparedQuery*>(prepared[i])); locks.emplace_back(queries.back()->mutex); }
+      std::vector<DeviceDatabase::FusedResult> results;
+      engine.runPreparedMany(queries, results);
+      for (uint32_t i = 0; i < n; ++i) texts[i] = capi::dupString(engine.responseText(queries[i]->query.action, queries[i]->names, results[i]));
+   });
+}
 // The response text of a prepared query (what silo_engine_execute returns for the same text)
 char* silo_prepared_run(void* engine_, void* prepared_) {
    char* out = nullptr;

@@ -523,6 +523,34 @@ class DeviceDatabase {
       runWithRowBuffers(p.names.size(), p.compiled.partitions.size(), result, [&](sb_sequence_rows* out, uint64_t* cards) { return sb_query_run(p.handle, out, cards); });
    }
 
+   // Several prepared queries as one batch from this thread (sb_query_run_many): enqueued together, collected together. A query
+   // whose rows did not fit its buffers is run again on its own.
+   void runPreparedMany(const std::vector<PreparedQuery*>& queries, std::vector<FusedResult>& results) const {
+      results.assign(queries.size(), FusedResult());
+      std::vector<sb_query*> handles;
+      std::vector<std::vector<sb_sequence_rows>> outs(queries.size());
+      std::vector<sb_sequence_rows*> out_ptrs;
+      std::vector<uint64_t*> card_ptrs;
+      std::vector<size_t> batch;      // index into `queries` of every query that has a device handle
+      for (size_t i = 0; i < queries.size(); ++i) {
+         PreparedQuery& p = *queries[i];
+         FusedResult& r = results[i];
+         r.sequences.resize(p.names.size());
+         r.cardinalities.assign(p.compiled.partitions.size(), 0);
+         if (!p.handle) continue;
+         for (auto& seq : r.sequences) seq.rows.resize(4096);
+         for (size_t k = 0; k < p.names.size(); ++k) outs[i].push_back(sb_sequence_rows{r.sequences[k].rows.data(), r.sequences[k].rows.size(), 0, 0, 0});
+         handles.push_back(p.handle); out_ptrs.push_back(outs[i].data()); card_ptrs.push_back(r.cardinalities.data()); batch.push_back(i);
+      }
+      if (!handles.empty()) check(sb_query_run_many(handles.data(), static_cast<uint32_t>(handles.size()), out_ptrs.data(), card_ptrs.data()));
+      for (size_t i : batch) {
+         bool fits = true;
+         for (size_t k = 0; k < outs[i].size(); ++k) fits = fits && outs[i][k].n_rows <= results[i].sequences[k].rows.size();
+         if (!fits) { runPrepared(*queries[i], results[i]); continue; }
+         for (size_t k = 0; k < outs[i].size(); ++k) { results[i].sequences[k].rows.resize(outs[i][k].n_rows); results[i].sequences[k].produced = outs[i][k].produced != 0; }
+      }
+   }
+
    QueryResult resultFromRows(const Action& action, const std::vector<std::string>& names, const FusedResult& fused) const {
       return action.executeAndOrder([&]() -> QueryResult {
          if (action.type == ActionType::AGGREGATED) {

@@ -70,6 +70,7 @@ def host():
         "silo_prepared_free": (None, [vp]),
         "silo_prepared_run_device": (ctypes.c_int, [vp, vp, ctypes.POINTER(u64)]),
         "silo_prepared_run": (vp, [vp, vp]),
+        "silo_prepared_run_many": (ctypes.c_int, [vp, ctypes.POINTER(vp), u32, ctypes.POINTER(vp)]),
         "silo_prepared_table": (ctypes.c_int, [vp, u32, vp, u64]),
         "silo_prepared_bytes": (ctypes.c_int, [vp, vp, u32, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
         "silo_prepared_elapsed_ms": (ctypes.c_float, [vp]),
@@ -498,6 +499,17 @@ def merge_partials(db, query, partial_texts):
     q = query if isinstance(query, str) else json.dumps(query)
     arr = (ctypes.c_char_p * max(len(partial_texts), 1))(*[t.encode() for t in partial_texts])
     return json.loads(_take_string(host().silo_merge_partials(db.handle, q.encode(), arr, len(partial_texts))))["queryResult"]
+
+
+def run_many(engine, prepared):
+    """a batch of Prepared queries from this thread (sb_query_run_many): every query is enqueued before the first is waited for;
+    returns their query results"""
+    n = len(prepared)
+    handles = (ctypes.c_void_p * max(n, 1))(*[p.handle for p in prepared])
+    texts = (ctypes.c_void_p * max(n, 1))()
+    if host().silo_prepared_run_many(engine.handle, handles, n, texts) != 0:
+        raise _error()
+    return [json.loads(_take_string(texts[i]))["queryResult"] for i in range(n)]
 
 
 def rows_from_table(db, query, sequence_name, counts):

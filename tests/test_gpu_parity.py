@@ -309,3 +309,18 @@ def test_in_library_reduce_single_rank(libs, synth_small):
         pysilo.comm_free(engine)
     finally:
         engine.close()
+
+
+def test_batch_of_prepared_queries_from_one_thread(libs, synth_medium, medium_engine):
+    """sb_query_run_many: the queries of a batch are enqueued together; every response equals the query run on its own"""
+    pysilo, oracle = libs
+    queries = [{"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": f} for f in synthetic_filters(synth_medium)[:5]]
+    queries.append({"action": {"type": "Aggregated"}, "filterExpression": synthetic_filters(synth_medium)[2]})
+    prepared = [pysilo.Prepared(medium_engine, q, use_graph=(k % 2 == 0)) for k, q in enumerate(queries)]
+    try:
+        for _ in range(2):
+            assert pysilo.run_many(medium_engine, prepared) == [medium_engine.execute(q) for q in queries]
+        assert pysilo.run_many(medium_engine, prepared[:1])[0] == oracle.execute(synth_medium, queries[0])
+    finally:
+        for p in prepared:
+            p.close()
