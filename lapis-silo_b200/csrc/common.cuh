@@ -73,7 +73,7 @@ constexpr uint32_t TILE_POSITIONS = 256;     // positions per tile (shared-memor
 constexpr uint32_t MAX_TILE_POSITIONS = 512;
 constexpr uint32_t SLAB_KEYS = 4;            // container keys per slab
 constexpr uint32_t SLAB_WORDS32 = SLAB_KEYS * 2048;   // 32-bit filter words per slab (32 KB)
-constexpr uint32_t FLAT_MAX = 64;            // containers up to this cardinality become postings (pool.cuh flatMax)
+constexpr uint32_t FLAT_MAX = 256;           // containers up to this cardinality become postings (pool.cuh flatMax)
 constexpr uint32_t POSTING_ROW_BITS = 18;
 constexpr uint32_t POSTING_ROW_MASK = (1u << POSTING_ROW_BITS) - 1u;
 

@@ -234,7 +234,7 @@ def test_concurrent_queries_are_isolated(libs, synth_medium, medium_engine):
 
 
 @pytest.mark.parametrize("env", [{"SB_K1_CTAS": "1"}, {"SB_K1_CTAS": "3"}, {"SB_K1_CTAS": "7"}, {"SB_K1_CTAS": "4000"}, {"SB_ITEM_CAP_KB": "4"},
-                                 {"SB_RUN_CAP_KB": "1"}, {"SB_RUN_CAP_KB": "4096"}, {"SB_TILE_POSITIONS": "512"}, {"SB_FLAT_MAX": "16"}, {"SB_FLAT_MAX": "256"}, {"SB_FLAT_MAX": "1024"},
+                                 {"SB_RUN_CAP_KB": "1"}, {"SB_RUN_CAP_KB": "4096"}, {"SB_TILE_POSITIONS": "512"}, {"SB_FLAT_MAX": "16"}, {"SB_FLAT_MAX": "64"}, {"SB_FLAT_MAX": "1024"},
                                  {"SB_K1_VARIANT": "1"}, {"SB_K1_VARIANT": "2", "SB_K1_CTAS": "5"}, {"SB_K1_VARIANT": "2", "SB_TILE_POSITIONS": "512", "SB_ITEM_CAP_KB": "4"}],
                          ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
 def test_scan_kernel_variants(libs, synth_small, synth_medium, env, monkeypatch):
