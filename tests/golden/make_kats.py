@@ -133,6 +133,12 @@ def main():
         exp = expected(body, "under_test")
         if m and exp is not None:
             cases.append({"name": name, "tree": {"op": "index_scan", "row_count": row_count(body) or 5, "ids": roarings(m.group(1))[0]}, "expected": exp})
+    for name, body in tests("bitmap_producer.test.cpp"):
+        m = re.search(r"const roaring::Roaring test_bitmap\((.*?)\);", body)
+        exp = expected(body, "under_test")
+        if m and exp is not None:
+            tree = {"op": "bitmap_producer", "row_count": row_count(body) or 5, "ids": roarings("roaring::Roaring(" + m.group(1) + ")")[0]}
+            cases.append({"name": name, "tree": dict(tree, negate=True) if ".negate()" in body else tree, "expected": exp})
     for name, body in tests("empty.test.cpp"):
         exp = expected(body, "under_test")
         if exp is not None:
