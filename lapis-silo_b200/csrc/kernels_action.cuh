@@ -7,7 +7,7 @@
 //                     |F| terms of the deleted / flipped symbols.
 //   k3_init_table     the table starts as the sum of the precomputed tables of the partitions whose filter is full
 //                     (mutations.cpp:101-136).
-//   classify_partitions / compact_items   Mutations::preFilterBitmaps (mutations.cpp:36-63) on the device: a query is one
+//   classify_partitions / compact_runs    Mutations::preFilterBitmaps (mutations.cpp:36-63) on the device: a query is one
 //                     submission, the host learns the cardinalities only with the result.
 // All arithmetic is uint32 with wrap-around, like the reference (mutations.cpp:75,80,94).
 #pragma once
@@ -50,15 +50,6 @@ __device__ __forceinline__ void mbarWait(uint64_t* bar, uint32_t parity) {
 
 // 128-bit load of data that is read once per query
 __device__ __forceinline__ uint4 loadStream(const uint4* p) { return __ldg(p); }
-
-// Adds `val` to base[idx] once per distinct idx among the lanes with pred set.
-__device__ __forceinline__ void warpAggregatedSharedAdd(uint32_t* base, uint32_t idx, int val, bool pred) {
-   const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
-   if (!pred) return;
-   const uint32_t peers = __match_any_sync(mask, idx);
-   const int total = __reduce_add_sync(peers, val);
-   if (laneId() == uint32_t(__ffs(peers) - 1) && total != 0) atomicAdd(&base[idx], uint32_t(total));
-}
 
 // |F ∩ [key*65536 + a, key*65536 + b]| through the rank tables (a <= b < 65536).
 __device__ __forceinline__ uint32_t filterRangeCount(const PartQuery& q, uint32_t key, uint32_t a, uint32_t b) {
@@ -282,8 +273,9 @@ k1_scan(const SeqDev s, const ActionPtrs a, uint32_t* __restrict__ counts, int f
       // thread 0 fetches the CTA's next item while the other warps stream
       if (threadIdx.x == 0) fetchNext(item_slots + (turn ^ 1u));
 
-      // Eight postings at a time: the eight filter words are fetched first (independent shared-memory loads), then the hits
-      // are counted with unconditional shared-memory increments -- no data-dependent branch, one load round trip per eight postings.
+      // Eight postings at a time: the eight filter words are fetched first (independent shared-memory loads: one round trip per
+      // eight postings), then the hits are counted -- FLAGS & 1: a reduction under a predicate; otherwise an unconditional
+      // increment of the posting's slot or, for a miss, of the lane's dummy slot.
       const uint32_t counts_s = smemAddr(tile_counts);
       auto probe8 = [&](const uint4& p0, const uint4& p1) {
          const uint32_t p[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};

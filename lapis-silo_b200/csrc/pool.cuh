@@ -140,7 +140,6 @@ struct Sequence {   // one logical sequence (store name) over all partitions of 
    DeviceBuffer<uint32_t> miss_tile_bits;
    DeviceBuffer<uint32_t> full_tables;   // [P][sigma * length]
    DeviceBuffer<uint8_t> reference;      // [length] symbols of the reference sequence (row selection)
-   DeviceBuffer<uint32_t> row_area;      // [4] counter + selected rows
    SeqDev dev{};
    uint32_t n_items = 0, n_slabs = 0, n_runs = 0;
    uint32_t k1_resident[8] = {1, 1, 1, 1, 1, 1, 1, 1};   // CTAs of k1_scan per SM, per compiled variant
