@@ -178,10 +178,9 @@ def cpu_baseline_line(db, query, rows):
 
 def run_reference(args, rank, world):
     """The reference arm: the CPU restatement of the reference's own algorithm on the host cores (rank 0 only). A whole query
-    takes minutes at 40 M rows, so a step is a bounded sample -- the selected partitions with the fewest filtered rows (at least
-    5 % of them) on the first 300 positions per host thread -- and value = (share of the query the sample is) / (step time),
-    the share being filtered rows x positions (see cpu_baseline_line for the evidence). --full-pass measures the share instead:
-    one pass of the whole query, partition by partition, in set-up."""
+    takes minutes at 40 M rows, so a step is a bounded sample -- one selected partition on the first 300 positions per host
+    thread -- and value = (share of the query the sample is) / (step time); the share comes from a short calibration pass over
+    every selected partition. --full-pass measures the share with one pass of the whole query instead (minutes)."""
     if rank != 0:
         return
     import pysilo
@@ -193,21 +192,28 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     filtered = {p: oracle_bind.filter_cardinality(db, query["filterExpression"], p) for p in db.owned}
     total_filtered = sum(filtered.values())
-    sample, seen = [], 0
-    for p in sorted((p for p in db.owned if filtered[p]), key=lambda p: filtered[p]):
-        sample.append(p)
-        seen += filtered[p]
-        if seen >= 0.05 * total_filtered:
-            break
+    selected = [p for p in db.owned if filtered[p]]
+    # Calibration (seconds, not minutes): every selected partition on a short prefix of the positions gives its WEIGHT in the
+    # query's CPU time. The per-partition cost is not a function of the filtered rows alone (measured full pass at 40 M rows,
+    # profiles/r02_reference_arm_40m_full_pass.json: 36-64 us per filtered row depending on the filter's density), so the
+    # share of a sample is measured, not derived; the cost is linear in the positions walked (same file: a partition on 16 %
+    # of the positions took 16.3 % of its full time).
+    calibration_positions = min(GENOME_LENGTH, 75 * cores)
+    weight = {p: oracle_bind.time_query_sample(db, query, [p], calibration_positions, threads=cores) for p in selected}
+    total_weight = sum(weight.values())
+    # a step = the cheapest partition that still carries at least 5 % of the query, on the first 300 positions per host thread
+    candidates = [p for p in selected if weight[p] >= 0.05 * total_weight] or selected
+    sample = [min(candidates, key=lambda p: weight[p])]
+    seen = sum(filtered[p] for p in sample)
     positions = min(GENOME_LENGTH, 300 * cores)
-    fraction = (seen / max(total_filtered, 1)) * (positions / GENOME_LENGTH)
-    fraction_source = "filtered rows x positions of the sample / of the query"
-    extra = {}
+    fraction = (sum(weight[p] for p in sample) / max(total_weight, 1e-12)) * (positions / GENOME_LENGTH)
+    fraction_source = f"measured weights of the selected partitions on {calibration_positions} positions x share of the positions"
+    extra = {"calibration": [{"partition": p, "rows": db.partition_rows(p), "filtered_rows": filtered[p], "weight": round(weight[p] / total_weight, 5)} for p in selected]}
     if args.full_pass:
         full, _, _, _, per_partition = cpu_calibrate(db, query)
         t_sample = oracle_bind.time_query_sample(db, query, sample, positions, threads=cores)
-        extra = {"full_pass_s": full, "analytic_fraction": fraction,
-                 "per_partition": [{"partition": p, "rows": db.partition_rows(p), "filtered_rows": filtered[p], "cpu_s": round(per_partition[p], 3)} for p in db.owned]}
+        extra.update({"full_pass_s": full, "calibrated_fraction": fraction,
+                      "per_partition": [{"partition": p, "rows": db.partition_rows(p), "filtered_rows": filtered[p], "cpu_s": round(per_partition[p], 3)} for p in db.owned]})
         fraction = t_sample / full
         fraction_source = "measured: sample time / time of one full pass over all partitions"
     setup_s = time.time() - t0
