@@ -47,6 +47,21 @@ int64_t silo_db_compare_stores(const void* a_, const void* b_) {
    });
    return differences;
 }
+// Test hook (tests/test_host_cpu.py): PangoLineageAliasLookup built from a JSON object {"alias": ["value", ...] | "value"},
+// applied to one lineage; direction 0 = unalias (pango_lineage_alias.cpp:25-47), 1 = alias (:49-79)
+char* silo_alias_apply(const char* alias_json, const char* lineage, int direction) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      PangoLineageAliasLookup lookup;
+      const json::Value j = json::parse(alias_json);
+      for (const auto& [key, value] : j.obj) {
+         if (value.is_array()) { std::vector<std::string> v; for (const auto& e : value.arr) v.push_back(e.as_string()); lookup.alias_key[key] = v; }
+         else if (value.is_string() && !value.s.empty()) lookup.alias_key[key] = {value.s};
+      }
+      out = capi::dupString(direction ? lookup.alias(lineage) : lookup.unalias(lineage));
+   });
+   return out;
+}
 void silo_db_free(void* db) { delete static_cast<Database*>(db); }
 uint32_t silo_db_partition_count(const void* db) { return static_cast<uint32_t>(static_cast<const Database*>(db)->partitions.size()); }
 uint32_t silo_db_partition_rows(const void* db, uint32_t p) { return static_cast<const Database*>(db)->partitions.at(p)->sequence_count; }

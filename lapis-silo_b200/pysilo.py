@@ -78,6 +78,7 @@ def host():
         "silo_engine_execute_sharded": (vp, [vp, cp, ctypes.c_int]),
         "silo_engine_execute_partial": (vp, [vp, cp]),
         "silo_merge_partials": (vp, [vp, cp, ctypes.POINTER(cp), u32]),
+        "silo_alias_apply": (vp, [cp, cp, ctypes.c_int]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32, u32]),
         "silo_synth_owned_count": (u32, [vp]),
         "silo_synth_owned": (u32, [vp, u32]),
@@ -499,6 +500,11 @@ def merge_partials(db, query, partial_texts):
     q = query if isinstance(query, str) else json.dumps(query)
     arr = (ctypes.c_char_p * max(len(partial_texts), 1))(*[t.encode() for t in partial_texts])
     return json.loads(_take_string(host().silo_merge_partials(db.handle, q.encode(), arr, len(partial_texts))))["queryResult"]
+
+
+def alias_apply(alias_map, lineage, alias=False):
+    """host PangoLineageAliasLookup (storage.hpp) built from {alias: [values]}: unalias(lineage), or alias(lineage) with alias=True"""
+    return _take_string(host().silo_alias_apply(json.dumps(alias_map).encode(), lineage.encode(), 1 if alias else 0))
 
 
 def run_many(engine, prepared):

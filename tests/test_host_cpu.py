@@ -108,3 +108,21 @@ def test_aggregated_partials_of_a_sharded_database_merge_to_the_whole(libs, synt
             partial["action"].pop(key, None)
         texts = [oracle.execute_subset_text(synth_small, partial, shard) for shard in shards]
         assert pysilo.merge_partials(synth_small, query, texts) == oracle.execute(synth_small, query)
+
+
+def test_pango_lineage_alias_lookup_on_the_reference_test_parameters(libs):
+    """host/storage.hpp PangoLineageAliasLookup against the parameter lists of the reference's own unit test
+    (src/silo/storage/pango_lineage_alias.test.cpp:31-42 unaliasPangoLineage, :61-74 aliasPangoLineage, :76-86 the alias file of exampleDataset)"""
+    pysilo, _ = libs
+    resolve_map = {"X": ["A"], "XY": ["A.1"]}
+    for lineage, want in [("", ""), ("SomeNotListedAlias", "SomeNotListedAlias"), ("X", "A"), ("XY", "A.1"), ("X.1.1", "A.1.1"), ("XYX.1.1", "XYX.1.1"), (".X", ".X")]:
+        assert pysilo.alias_apply(resolve_map, lineage) == want
+    unresolve_map = {"BA": ["B.1.1.529"], "BC": ["B.1.1.529.1.1.1"], "XA": ["B.1.1.7", "B.1.177"]}
+    for lineage, want in [("", ""), ("SomeNotListedAlias", "SomeNotListedAlias"), ("B.1.1.529", "B.1.1.529"), ("B.1.1.529.1", "BA.1"), ("B.1.1.529.1.1", "BA.1.1"),
+                          ("B.1.1.529.1.1.1", "BA.1.1.1"), ("B.1.1.529.1.1.1.1.1.1.1.1", "BC.1.1.1.1.1"), ("XA.1.1", "XA.1.1"), ("XA.1.1.1.1.1.1.1", "XA.1.1.1.1.1.1.1")]:
+        assert pysilo.alias_apply(unresolve_map, lineage, alias=True) == want
+    import json
+    from pathlib import Path
+    from_file = json.loads((Path(__file__).parent / "golden" / "exampleDataset" / "pangolineage_alias.json").read_text())
+    for lineage, want in [("B", "B"), ("B.1", "B.1"), ("B.1.2", "B.1.2"), ("C", "B.1.1.1"), ("EP", "B.1.1.529.2.75.3.1.1.4")]:
+        assert pysilo.alias_apply(from_file, lineage) == want
