@@ -3,6 +3,8 @@
 Copies DATA, never source code:
   * exampleDataset/            the reference's 100-sequence test dataset inputs (testBaseData/exampleDataset)
   * exampleDataset1000Sequences/  BASELINE config C1 inputs
+  * fastaFilesWithMissingSequences/, ndjsonWithNullSequences/, ndjsonWithSqlKeywordField/, tsvWithSqlKeywordField/
+                               the four tiny input directories of preprocessing/preprocessor.test.cpp (whole directories)
   * queries/*.json             the end-to-end golden vectors of endToEndTests/test/queries that are on the
                                hot path (Aggregated with and without groupByFields, Mutations, AminoAcidMutations)
   * invalidQueries/*.json      the invalid-query fixtures (expected HTTP 400 message)
@@ -24,6 +26,7 @@ DATASET_FILES = {
         "database_config.yaml", "preprocessing_config.yaml", "reference_genomes.json", "pangolineage_alias.json", "sample.ndjson.zst",
     ],
 }
+WHOLE_DATASETS = ["fastaFilesWithMissingSequences", "ndjsonWithNullSequences", "ndjsonWithSqlKeywordField", "tsvWithSqlKeywordField"]
 HOT_ACTIONS = {"Mutations", "AminoAcidMutations", "Aggregated"}
 
 
@@ -33,6 +36,11 @@ def main():
         dst.mkdir(exist_ok=True)
         for f in files:
             shutil.copyfile(REF / "testBaseData" / name / f, dst / f)
+    for name in WHOLE_DATASETS:
+        dst = OUT / name
+        dst.mkdir(exist_ok=True)
+        for f in sorted((REF / "testBaseData" / name).iterdir()):
+            shutil.copyfile(f, dst / f.name)
     skipped = []
     for sub in ["queries", "invalidQueries"]:
         dst = OUT / sub
