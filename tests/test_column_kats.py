@@ -5,6 +5,10 @@ for what the unit test reads off the column with a filter (-> row ids) or with A
   indexed_string_column.test.cpp:9-48   filter, values
   string.test.cpp:62-96                 equality of strings that agree on a prefix of up to 32 characters
   date.test.cpp:7-31                    stringToDate / dateToString
+  insertion_column.test.cpp:31-62       search(sequence, position, pattern)
+  string_column.test.cpp:8-25           values come back as inserted
+and, worked out by hand from int_between.cpp / int_equals.cpp / float_between.cpp / float_equals.cpp, the null and
+bound rules of the numeric selections.
 The CPU tests pin the oracle on these answers, the GPU tests the device path on the same ones."""
 import json
 from pathlib import Path
@@ -191,3 +195,63 @@ def test_sorted_date_column_takes_the_range_selection(libs, backend, tmp_path):
     assert b.ids(between("2023-01-02", None)) == []
     assert b.ids(between(None, None)) == [2, 3, 4, 5, 6] and keys({"type": "Not", "child": between(None, None)}) == ["k0004", "k0006"]
     assert grouped_values(b, "date") == [(None, 2), ("0012-12-12", 1), ("2010-12-03", 2), ("2020-01-01", 1), ("2023-01-01", 1)]
+
+
+def test_insertion_column_search(libs, backend, tmp_path):
+    """insertion_column.test.cpp:31-62"""
+    rows = ["25701:ACCA", "25701:CCG", "25701:CCG", "25701:TTACAT,25701:ACCA", "25701:ACCA", "25701:TTACAT,25701:ACCA,25701:AGCTGTTCAG"]
+    b = backend(make_db(libs[0], tmp_path, "nucleotideInsertions", "      type: insertion\n", rows))
+    search = lambda position, pattern: {"type": "InsertionContains", "column": "nucleotideInsertions", "sequenceName": "main", "position": position, "value": pattern}
+    assert b.ids(search(25701, ".*CC.*")) == [0, 1, 2, 3, 4, 5]
+    assert b.ids(search(25701, ".*TTA.*CAT.*")) == [3, 5]
+    assert b.ids(search(25701, ".*AGC.*TGT.*TCA.*G.*")) == [5]
+    assert b.ids(search(25701, ".*AGC.*TG.*T.*T.*C.*AG.*")) == [5]
+    assert b.ids(search(25701, ".*TTT.*AAA.*")) == []
+    assert b.ids(search(100, ".*TTT.*AAA.*")) == []
+    assert b.ids(search(100, ".*CC.*")) == []
+    without_name = {"type": "InsertionContains", "column": "nucleotideInsertions", "position": 25701, "value": ".*TTA.*CAT.*"}      # the default sequence
+    assert b.ids(without_name) == [3, 5]
+
+
+def test_string_column_values_come_back(libs, backend, tmp_path):
+    """string_column.test.cpp:8-25"""
+    rows = ["value 1", "value 2", "value 2", "value 3", "some string that is a little longer 1", "value 1"]
+    b = backend(make_db(libs[0], tmp_path, "name", "      type: string\n", rows))
+    for value in set(rows):
+        assert b.ids({"type": "StringEquals", "column": "name", "value": value}) == [r for r, v in enumerate(rows) if v == value]
+    assert grouped_values(b, "name") == [("some string that is a little longer 1", 1), ("value 1", 2), ("value 2", 2), ("value 3", 1)]
+
+
+def test_int_selections(libs, backend, tmp_path):
+    """int_equals.cpp:65 (null = INT32_MIN), int_between.cpp:41-48 (lower bound INT32_MIN + 1 when open -> nulls never match; upper bound inclusive)"""
+    rows = ["4", "50", "", "51", "-3", "50", "0"]
+    b = backend(make_db(libs[0], tmp_path, "age", "      type: int\n", rows))
+    equals = lambda v: {"type": "IntEquals", "column": "age", "value": v}
+    between = lambda lo, hi: {"type": "IntBetween", "column": "age", "from": lo, "to": hi}
+    assert b.ids(equals(50)) == [1, 5] and b.ids(equals(0)) == [6] and b.ids(equals(7)) == []
+    assert b.ids(equals(None)) == [2]
+    assert b.ids(between(4, 50)) == [0, 1, 5]
+    assert b.ids(between(None, 4)) == [0, 4, 6]
+    assert b.ids(between(50, None)) == [1, 3, 5]
+    assert b.ids(between(None, None)) == [0, 1, 3, 4, 5, 6]
+    assert b.ids(between(51, 50)) == []
+    assert b.ids({"type": "Not", "child": between(None, None)}) == [2]
+    assert grouped_values(b, "age") == [(None, 1), (-3, 1), (0, 1), (4, 1), (50, 2), (51, 1)]
+
+
+def test_float_selections(libs, backend, tmp_path):
+    """float_equals.cpp:67 (null = NaN, equal to nothing), float_between.cpp:46-62 (>= from, < to: the upper bound is exclusive; no bounds at
+    all is "!= NaN", true for every row, nulls included)"""
+    rows = ["0.5", "0.9", "", "0.98", "0.5", "0.0", "-1.5"]
+    b = backend(make_db(libs[0], tmp_path, "qc", "      type: float\n", rows))
+    equals = lambda v: {"type": "FloatEquals", "column": "qc", "value": v}
+    between = lambda lo, hi: {"type": "FloatBetween", "column": "qc", "from": lo, "to": hi}
+    assert b.ids(equals(0.5)) == [0, 4] and b.ids(equals(0.0)) == [5] and b.ids(equals(0.51)) == []
+    assert b.ids(equals(None)) == []
+    assert b.ids(between(0.5, 0.98)) == [0, 1, 4]
+    assert b.ids(between(0.5, 0.5)) == []
+    assert b.ids(between(None, 0.5)) == [5, 6]
+    assert b.ids(between(0.9, None)) == [1, 3]
+    assert b.ids(between(None, None)) == [0, 1, 2, 3, 4, 5, 6]
+    assert b.ids({"type": "Not", "child": between(-100.0, 100.0)}) == [2]
+    assert grouped_values(b, "qc") == [(None, 1), (-1.5, 1), (0.0, 1), (0.5, 2), (0.9, 1), (0.98, 1)]
