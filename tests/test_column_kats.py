@@ -254,4 +254,13 @@ def test_float_selections(libs, backend, tmp_path):
     assert b.ids(between(0.9, None)) == [1, 3]
     assert b.ids(between(None, None)) == [0, 1, 2, 3, 4, 5, 6]
     assert b.ids({"type": "Not", "child": between(-100.0, 100.0)}) == [2]
+    # Not of a Selection with ONE predicate inverts the comparator instead of complementing (selection.cpp:127-132, :201-224): the null
+    # row, NaN, compares false both ways and is lost; with two predicates it is a Complement and the null row comes back (line above)
+    assert b.ids({"type": "Not", "child": between(None, 0.9)}) == [1, 3]
+    assert b.ids({"type": "Not", "child": between(0.5, None)}) == [5, 6]
+    assert b.ids({"type": "Not", "child": {"type": "Not", "child": between(0.5, None)}}) == [0, 1, 3, 4]
+    assert b.ids({"type": "Not", "child": {"type": "And", "children": [between(0.5, None), {"type": "True"}]}}) == [5, 6]
+    assert b.ids({"type": "Not", "child": between(None, None)}) == []
+    assert b.ids({"type": "Not", "child": equals(0.5)}) == [1, 2, 3, 5, 6]      # != is true for NaN
+    assert b.ids({"type": "Not", "child": equals(None)}) == [0, 1, 2, 3, 4, 5, 6]
     assert grouped_values(b, "qc") == [(None, 1), (-1.5, 1), (0.0, 1), (0.5, 2), (0.9, 1), (0.98, 1)]
