@@ -5,6 +5,9 @@ symbols, Selection / Intersection merging, De Morgan rewrites, Full / Empty shor
 path share. Here the expected row set of an expression does not come from that code: `matches()` below decides for ONE ROW whether
 the expression holds, from the row's strings and values, carrying the ambiguity mode down the tree the way Expression::compile does
 (expression.cpp:38-46, negation.cpp:32, maybe.cpp, exact.cpp). 48 random rows, several hundred random trees of depth <= 4.
+The Mutations / AminoAcidMutations actions get the same treatment: `mutation_rows()` counts symbols over the rows the model selects and
+applies the output rule of mutations.cpp:184-229 (coverage over the valid mutation symbols only, count > ceil(total * p) - 1, the
+reference symbol never printed, positions ascending and symbols in VALID_MUTATION_SYMBOLS order).
 CPU: oracle. GPU: device path."""
 import json
 import random
@@ -203,3 +206,70 @@ def test_random_trees_against_the_model(ids, model_db, seed):
         assert ids(e) == want, json.dumps(e)
         nonempty += 0 < len(want) < N_ROWS
     assert nonempty > 40
+
+
+VALID = {"nuc": "-ACGT", "gene": "-ACDEFGHIKLMNPQRSTVWY*"}      # nucleotide_symbols.h / aa_symbols.h:56-79, in output order
+
+
+def mutation_rows(rows, flt, kind, sequence_name, reference, min_proportion):
+    import math
+    selected = [r for r in rows if matches(flt, r)]
+    out = []
+    for pos, ref in enumerate(reference):
+        counts = {sym: sum(r[kind][pos] == sym for r in selected) for sym in VALID[kind]}
+        total = sum(counts.values())
+        if total == 0:
+            continue
+        threshold = 0 if min_proportion == 0 else math.ceil(total * min_proportion) - 1
+        for sym in VALID[kind]:
+            if sym != ref and counts[sym] > threshold:
+                out.append({"count": counts[sym], "mutation": f"{ref}{pos + 1}{sym}", "proportion": counts[sym] / total, "sequenceName": sequence_name})
+    return out
+
+
+@pytest.fixture(params=BACKENDS)
+def execute(request, libs, model_db):
+    pysilo, oracle = libs
+    db, _ = model_db
+    if request.param == "oracle":
+        yield lambda query: oracle.execute(db, query)
+    else:
+        engine = pysilo.Engine(db, 0)
+        yield engine.execute
+        engine.close()
+
+
+def test_mutation_actions_against_the_model(execute, model_db):
+    _, rows = model_db
+    rng = random.Random(99)
+    filters = [{"type": "True"}, {"type": "False"}] + [random_tree(rng, rng.randint(0, 3)) for _ in range(60)]
+    emitted = 0
+    for k, flt in enumerate(filters):
+        for min_proportion in ((0.05, 1.0) if k % 2 else (0.3, 0.0)):
+            for action, kind, name, reference in (("Mutations", "nuc", "main", NUC_REF), ("AminoAcidMutations", "gene", "G", GENE_REF)):
+                query = {"action": {"type": action, "sequenceName": name, "minProportion": min_proportion}, "filterExpression": flt}
+                want = mutation_rows(rows, flt, kind, name, reference, min_proportion)
+                assert execute(query) == want, json.dumps(query)
+                emitted += len(want)
+        assert execute({"action": {"type": "Aggregated"}, "filterExpression": flt}) == [{"count": sum(matches(flt, r) for r in rows)}]
+    assert emitted > 500
+
+
+def test_grouped_counts_against_the_model(execute, model_db):
+    """Aggregated with groupByFields: one output row per distinct tuple of the selected rows (aggregated.cpp:100-149), null for the empty
+    string / missing number / missing date (tuple.cpp), ordered by the group-by fields with nulls first"""
+    from collections import Counter
+    _, rows = model_db
+    rng = random.Random(5)
+    column_of = {"age": "age", "qc": "qc", "region": "region", "name": "name", "lineage": "lineage", "date": "date"}
+    shown = lambda v: None if v in ("", None) else v
+    for _ in range(40):
+        fields = rng.sample(sorted(column_of), rng.randint(1, 4))
+        flt = random_tree(rng, rng.randint(0, 2))
+        groups = Counter(tuple(shown(r[column_of[f]]) for f in fields) for r in rows if matches(flt, r))
+        ordered = sorted(groups.items(), key=lambda kv: [(v is not None, v) for v in kv[0]])
+        want = [dict(zip(fields, key), count=count) for key, count in ordered]
+        query = {"action": {"type": "Aggregated", "groupByFields": fields, "orderByFields": fields}, "filterExpression": flt}
+        assert execute(query) == want, json.dumps(query)
+        limited = dict(query, action=dict(query["action"], limit=3, offset=1))
+        assert execute(limited) == want[1:4]
