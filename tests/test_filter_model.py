@@ -41,14 +41,11 @@ def make_rows(rng):
     return rows
 
 
-@pytest.fixture(scope="module")
-def model_db(libs, tmp_path_factory):
-    rows = make_rows(random.Random(20240511))
-    d = tmp_path_factory.mktemp("filter_model")
+def build_db(libs, d, rows, schema_tail=""):
     (d / "database_config.yaml").write_text(
         "schema:\n  instanceName: model\n  metadata:\n    - name: key\n      type: string\n    - name: age\n      type: int\n    - name: qc\n      type: float\n"
         "    - name: region\n      type: string\n      generateIndex: true\n    - name: name\n      type: string\n"
-        "    - name: lineage\n      type: pango_lineage\n    - name: date\n      type: date\n  primaryKey: key\n")
+        "    - name: lineage\n      type: pango_lineage\n    - name: date\n      type: date\n  primaryKey: key\n" + schema_tail)
     (d / "preprocessing_config.yaml").write_text('metadataFilename: "metadata.tsv"\nreferenceGenomeFilename: "reference_genomes.json"\n')
     (d / "reference_genomes.json").write_text(json.dumps({"nucleotideSequences": [{"name": "main", "sequence": NUC_REF}], "genes": [{"name": "G", "sequence": GENE_REF}]}))
     text = lambda v: "" if v is None else str(v)
@@ -56,7 +53,13 @@ def model_db(libs, tmp_path_factory):
         "\t".join([r["key"], text(r["age"]), text(r["qc"]), r["region"], r["name"], r["lineage"], r["date"]]) + "\n" for r in rows))
     (d / "nuc_main.fasta").write_text("".join(f">{r['key']}\n{r['nuc']}\n" for r in rows))
     (d / "gene_G.fasta").write_text("".join(f">{r['key']}\n{r['gene']}\n" for r in rows))
-    return libs[0].Database.from_directory(d), rows
+    return libs[0].Database.from_directory(d)
+
+
+@pytest.fixture(scope="module")
+def model_db(libs, tmp_path_factory):
+    rows = make_rows(random.Random(20240511))
+    return build_db(libs, tmp_path_factory.mktemp("filter_model"), rows), rows
 
 
 def swapped(mode):
@@ -115,8 +118,9 @@ def matches(e, row, mode="NONE"):
     if t == "PangoLineage":
         want, have = e["value"].upper(), row["lineage"]
         return have == want or (e["includeSublineages"] and have.startswith(want + ".") and want != "")
-    if t == "DateBetween":      # the column is not the one rows are ordered by: >= from, < to (quirk Q14)
-        return row["date"] != "" and (e["from"] is None or row["date"] >= e["from"]) and (e["to"] is None or row["date"] < e["to"])
+    if t == "DateBetween":      # quirk Q14: on a column rows are not ordered by >= from, < to; on the dateToSortBy column `to` is inclusive
+        below_to = (lambda d: d <= e["to"]) if row.get("date_is_sorted") else (lambda d: d < e["to"])
+        return row["date"] != "" and (e["from"] is None or row["date"] >= e["from"]) and (e["to"] is None or below_to(row["date"]))
     raise AssertionError(t)
 
 
@@ -273,3 +277,53 @@ def test_grouped_counts_against_the_model(execute, model_db):
         assert execute(query) == want, json.dumps(query)
         limited = dict(query, action=dict(query["action"], limit=3, offset=1))
         assert execute(limited) == want[1:4]
+
+
+@pytest.fixture(scope="module")
+def partitioned_db(libs, tmp_path_factory):
+    """the same kind of rows, 300 of them, partitioned by lineage (preprocessor.cpp:159-199: here 8 partitions) and ordered by date inside
+    each partition: flipped and deleted symbols differ from partition to partition, DateBetween takes the RangeSelection"""
+    global N_ROWS
+    keep, N_ROWS = N_ROWS, 300
+    try:
+        rows = make_rows(random.Random(77))
+    finally:
+        N_ROWS = keep
+    for r in rows:
+        r["date_is_sorted"] = True
+    db = build_db(libs, tmp_path_factory.mktemp("filter_model_partitioned"), rows, "  dateToSortBy: date\n  partitionBy: lineage\n")
+    assert db.n_partitions >= 5
+    return db, rows
+
+
+@pytest.fixture(params=BACKENDS)
+def execute_partitioned(request, libs, partitioned_db):
+    pysilo, oracle = libs
+    db, _ = partitioned_db
+    if request.param == "oracle":
+        yield lambda query: oracle.execute(db, query)
+    else:
+        engine = pysilo.Engine(db, 0)
+        yield engine.execute
+        engine.close()
+
+
+def test_actions_over_several_partitions_against_the_model(execute_partitioned, partitioned_db):
+    from collections import Counter
+    _, rows = partitioned_db
+    rng = random.Random(4242)
+    date_filters = [{"type": "DateBetween", "column": "date", "from": lo, "to": hi} for lo, hi in
+                    ((None, None), ("2020-06-15", "2021-03-03"), (None, "2020-06-15"), ("2021-03-03", None), ("2021-03-04", "2022-12-30"), ("2020-06-15", "2020-06-15"))]
+    filters = [{"type": "True"}] + date_filters + [{"type": "Not", "child": f} for f in date_filters[:3]] + [random_tree(rng, rng.randint(0, 3)) for _ in range(50)]
+    shown = lambda v: None if v in ("", None) else v
+    for k, flt in enumerate(filters):
+        selected = [r for r in rows if matches(flt, r)]
+        assert execute_partitioned({"action": {"type": "Aggregated"}, "filterExpression": flt}) == [{"count": len(selected)}], json.dumps(flt)
+        min_proportion = (0.02, 0.5, 0.0)[k % 3]
+        for action, kind, name, reference in (("Mutations", "nuc", "main", NUC_REF), ("AminoAcidMutations", "gene", "G", GENE_REF)):
+            query = {"action": {"type": action, "sequenceName": name, "minProportion": min_proportion}, "filterExpression": flt}
+            assert execute_partitioned(query) == mutation_rows(rows, flt, kind, name, reference, min_proportion), json.dumps(query)
+        fields = rng.sample(["age", "qc", "region", "name", "lineage", "date"], rng.randint(1, 3))
+        groups = Counter(tuple(shown(r[f]) for f in fields) for r in selected)
+        want = [dict(zip(fields, key), count=count) for key, count in sorted(groups.items(), key=lambda kv: [(v is not None, v) for v in kv[0]])]
+        assert execute_partitioned({"action": {"type": "Aggregated", "groupByFields": fields, "orderByFields": fields}, "filterExpression": flt}) == want
