@@ -116,3 +116,33 @@ def test_uint32_wrap_survives_the_int32_sum():
     b = np.array([0x20, 0xFFFFFFFF, 0x80000000], dtype=np.uint32)
     s = (torch.from_numpy(a.view(np.int32).copy()) + torch.from_numpy(b.view(np.int32).copy())).numpy().view(np.uint32)
     assert s.tolist() == [0x10, 4, 0]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_row_sliced_shards_add_up_to_the_whole_database(libs, world):
+    """bench.py --shard rows (the default for N > 1): every lineage partition is cut into `world` row slices, slice k on rank k.
+    Each rank's database is built here in turn (host logic only), its local table and count come from the oracle over the partitions
+    the rank owns; the sums over the ranks must be the whole database's table and count -- for the world sizes of the scaling run."""
+    pysilo, oracle = libs
+    n_rows, genome = 12000, 1500
+    whole = pysilo.Database.synthetic(n_rows, SEED, genome_length=genome)
+    clade = whole.clade_mutations()
+    picks = [clade[(5 * k) % len(clade)] for k in range(8)]
+    flt = {"type": "N-Of", "numberOfMatchers": 1, "matchExactly": False, "children": [{"type": "NucleotideEquals", "position": p + 1, "symbol": s} for p, s in picks]}
+    query = {"action": {"type": "Mutations", "minProportion": 0.02}, "filterExpression": flt}
+    want_table, produced = oracle.mutation_counts(whole, query, "main", 16 * genome)
+    want_count = oracle.execute(whole, {"action": {"type": "Aggregated"}, "filterExpression": flt})[0]["count"]
+    assert produced and want_count > 0
+    table, count, rows, loads = np.zeros(16 * genome, dtype=np.uint64), 0, 0, []
+    for rank in range(world):
+        shard = pysilo.Database.synthetic(n_rows, SEED, genome_length=genome, world=world, rank=rank, row_slices=world)
+        assert shard.n_partitions == whole.n_partitions * world and len(shard.owned) == whole.n_partitions
+        local, _ = oracle.mutation_counts_subset(shard, query, "main", 16 * genome, shard.owned)
+        table += local
+        count += sum(oracle.filter_cardinality(shard, flt, p) for p in shard.owned)
+        loads.append(sum(shard.partition_rows(p) for p in shard.owned))
+        rows += loads[-1]
+        shard.close()
+    assert rows == n_rows and max(loads) - min(loads) <= whole.n_partitions      # slices differ by at most one row per lineage
+    assert count == want_count
+    assert np.array_equal(table, want_table.astype(np.uint64))
