@@ -327,3 +327,33 @@ def test_actions_over_several_partitions_against_the_model(execute_partitioned, 
         groups = Counter(tuple(shown(r[f]) for f in fields) for r in selected)
         want = [dict(zip(fields, key), count=count) for key, count in sorted(groups.items(), key=lambda kv: [(v is not None, v) for v in kv[0]])]
         assert execute_partitioned({"action": {"type": "Aggregated", "groupByFields": fields, "orderByFields": fields}, "filterExpression": flt}) == want
+
+
+def test_wide_and_deep_trees_against_the_model(ids, model_db):
+    """N-Of over 60 children with up to 61 matchers, and right-deep alternations of And / Or / N-Of 40 levels down: the evaluation stack
+    of the device interpreter outgrows shared memory (more than 24 planes) and moves to global memory (eval_plans<true>)"""
+    _, rows = model_db
+    rng = random.Random(31337)
+    check = lambda e: ids(e) == [r for r in range(N_ROWS) if matches(e, rows[r])]
+    for trial in range(3):
+        children = [random_leaf(rng) for _ in range(60)]
+        per_row = sorted(sum(matches(c, r) for c in children) for r in rows)
+        for k in sorted({0, 1, per_row[0], per_row[len(per_row) // 2], per_row[-1], per_row[-1] + 1, 24, 25, 26, 30, 47, 48, 59, 60, 61}):
+            for exactly in (False, True):
+                e = {"type": "N-Of", "numberOfMatchers": k, "matchExactly": exactly, "children": children}
+                assert check(e), (trial, k, exactly)
+                assert check({"type": "Not", "child": e}) and check({"type": "Maybe", "child": e})
+    for trial in range(6):
+        e = random_leaf(rng)
+        for level in range(40):
+            other = [random_tree(rng, 1) for _ in range(rng.randint(1, 2))]
+            kind = (level + trial) % 3
+            if kind == 0:
+                e = {"type": "And", "children": other + [e]}
+            elif kind == 1:
+                e = {"type": "Or", "children": other + [e]}
+            else:
+                e = {"type": "N-Of", "numberOfMatchers": 1 + level % 2, "matchExactly": level % 4 == 0, "children": other + [e]}
+            if level % 7 == 6:
+                e = {"type": "Not", "child": e}
+        assert check(e), trial
