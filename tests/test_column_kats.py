@@ -264,3 +264,19 @@ def test_float_selections(libs, backend, tmp_path):
     assert b.ids({"type": "Not", "child": equals(0.5)}) == [1, 2, 3, 5, 6]      # != is true for NaN
     assert b.ids({"type": "Not", "child": equals(None)}) == [0, 1, 2, 3, 4, 5, 6]
     assert grouped_values(b, "qc") == [(None, 1), (-1.5, 1), (0.0, 1), (0.5, 2), (0.9, 1), (0.98, 1)]
+
+
+def test_a_database_without_rows(libs, backend, tmp_path):
+    """no input rows at all: one partition of zero sequences; every action answers, nothing is counted, nothing divides by zero
+    (aggregated.cpp:58-66 sums no cardinalities, mutations.cpp:36-63 keeps no partition, tuple maps stay empty)"""
+    db = make_db(libs[0], tmp_path, "age", "      type: int\n", [])
+    assert db.n_partitions == 1 and db.info()["sequenceCount"] == 0
+    b = backend(db)
+    everything, nothing = {"type": "True"}, {"type": "Not", "child": {"type": "True"}}
+    leaf = {"type": "NucleotideEquals", "position": 1, "symbol": "A"}
+    for flt in (everything, nothing, leaf, {"type": "Not", "child": leaf}, {"type": "IntBetween", "column": "age", "from": None, "to": 5},
+                {"type": "N-Of", "numberOfMatchers": 1, "matchExactly": True, "children": [leaf, everything]}):
+        assert b.ids(flt) == []
+        assert b.execute({"action": {"type": "Aggregated"}, "filterExpression": flt}) == [{"count": 0}]
+        assert b.execute({"action": {"type": "Aggregated", "groupByFields": ["age"], "orderByFields": ["age"]}, "filterExpression": flt}) == []
+        assert b.execute({"action": {"type": "Mutations", "minProportion": 0.05}, "filterExpression": flt}) == []
