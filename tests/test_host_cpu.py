@@ -126,3 +126,50 @@ def test_pango_lineage_alias_lookup_on_the_reference_test_parameters(libs):
     from_file = json.loads((Path(__file__).parent / "golden" / "exampleDataset" / "pangolineage_alias.json").read_text())
     for lineage, want in [("B", "B"), ("B.1", "B.1"), ("B.1.2", "B.1.2"), ("C", "B.1.1.1"), ("EP", "B.1.1.529.2.75.3.1.1.4")]:
         assert pysilo.alias_apply(from_file, lineage) == want
+
+
+def test_query_error_messages_are_the_reference_s(libs, example_db):
+    """the 111 validation texts of the reference's query parser (tests/golden/query_error_messages.json, extracted by make_messages.py):
+    each is either a literal of the host's parser, or -- where the host composes the text from the expression's name -- produced by
+    the query below that provokes it (QueryParseException -> "parse:<text>", HTTP 400 in the reference)"""
+    import glob
+    import json
+    import re
+    from pathlib import Path
+    pysilo, oracle = libs
+    root = Path(__file__).resolve().parent
+    messages = json.loads((root / "golden" / "query_error_messages.json").read_text())
+    host = re.sub(r'"\s*\n\s*"', "", "".join(Path(f).read_text() for f in glob.glob(str(root.parent / "lapis-silo_b200" / "host" / "*.hpp"))))
+    provoked = {
+        "The field 'child' is required in a Not expression": {"type": "Not"},
+        "The field 'child' is required in a Maybe expression": {"type": "Maybe"},
+        "The field 'child' is required in a Exact expression": {"type": "Exact"},
+        "The field 'children' is required in an And expression": {"type": "And"},
+        "The field 'children' in an And expression needs to be an array": {"type": "And", "children": {}},
+        "The field 'children' is required in an Or expression": {"type": "Or"},
+        "The field 'children' in an Or expression needs to be an array": {"type": "Or", "children": "x"},
+        "The field 'children' is required in an N-Of expression": {"type": "N-Of", "numberOfMatchers": 1, "matchExactly": False},
+        "The field 'children' in an N-Of expression needs to be an array": {"type": "N-Of", "numberOfMatchers": 1, "matchExactly": False, "children": 3},
+        "The field 'position' is required in a NucleotideEquals expression": {"type": "NucleotideEquals", "symbol": "A"},
+        "The field 'position' in a NucleotideEquals expression needs to be an unsigned integer greater than 0": {"type": "NucleotideEquals", "position": "1", "symbol": "A"},
+        "The field 'position' is required in a AminoAcidEquals expression": {"type": "AminoAcidEquals", "sequenceName": "S", "symbol": "A"},
+        "The field 'position' in a AminoAcidEquals expression needs to be an unsigned integer greater than 0": {"type": "AminoAcidEquals", "sequenceName": "S", "position": 0, "symbol": "A"},
+        "The field 'position' is required in a HasNucleotideMutation expression": {"type": "HasNucleotideMutation"},
+        "The field 'position' in a HasNucleotideMutation expression needs to be an unsigned integer": {"type": "HasNucleotideMutation", "position": -1},
+        "The field 'position' is required in a HasAminoAcidMutation expression": {"type": "HasAminoAcidMutation", "sequenceName": "S"},
+        "The field 'position' in a HasAminoAcidMutation expression needs to be an unsigned integer": {"type": "HasAminoAcidMutation", "sequenceName": "S", "position": 1.5},
+        "The field 'value' in the InsertionContains expression does not contain a valid regex pattern": {"type": "InsertionContains", "column": "nucleotideInsertions", "position": 1, "value": "A(("},
+    }
+    assert len(messages) == 111
+    literal = 0
+    for m in messages:
+        if m["text"] in host:
+            literal += 1
+            continue
+        assert m["text"] in provoked, m
+        with pytest.raises(oracle.OracleError) as err:
+            oracle.execute(example_db, {"action": {"type": "Aggregated"}, "filterExpression": provoked[m["text"]]})
+        assert err.value.kind == "parse" and err.value.message.startswith(m["text"]), (m, str(err.value))
+        if "regex" not in m["text"]:
+            assert err.value.message == m["text"]
+    assert literal >= 90
