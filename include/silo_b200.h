@@ -122,6 +122,11 @@ int sb_result_cardinality(const sb_result* r, uint64_t* cardinality);
 /* Ascending row ids (what iterating the reference's OperatorResult yields). Call with out == NULL
  * to get the count. Needed by the host-side actions that stay outside the hot path. */
 int sb_result_export_ids(const sb_result* r, uint32_t* out, size_t capacity, size_t* n);
+/* The same row set as CRoaring portable bytes, i.e. what roaring::Roaring::readSafe (roaring_serialize.h:44) turns back into the
+ * bitmap an OperatorResult holds (operator_result.h:9-32) -- for host-side actions that want a roaring, not an id list. Array
+ * containers up to 4,096 values, bitset containers above, no run containers (the reader does not care; the caller may
+ * runOptimize). Call with out == NULL to get the size. */
+int sb_result_export_portable(const sb_result* r, void* out, size_t capacity, size_t* n_bytes);
 int sb_result_free(sb_result* r);
 
 /* ---- actions: replace Action::execute (query_engine.cpp:60) ------------------------------------ */

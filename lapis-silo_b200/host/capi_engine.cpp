@@ -83,6 +83,38 @@ int silo_engine_filter_ids(void* engine_, const char* filter_json, uint32_t loca
    });
 }
 
+// The same filter as CRoaring portable bytes (sb_result_export_portable): what a host-side action of the reference would readSafe
+int silo_engine_filter_portable(void* engine_, const char* filter_json, uint32_t local_partition, uint8_t** bytes, size_t* n) {
+   return capi::guarded([&] {
+      auto& engine = *static_cast<DeviceDatabase*>(engine_);
+      auto expression = filter::parseExpression(json::parse(filter_json));
+      auto op = expression->compile(engine.db, *engine.db.partitions.at(engine.owned.at(local_partition)), filter::AmbiguityMode::NONE);
+      DeviceDatabase::Plan plan;
+      engine.lower(*op, local_partition, plan);
+      DeviceDatabase::EvaluatedFilters filters;
+      filters.handle = engine.handle;
+      filters.partitions = {local_partition};
+      filters.results = {nullptr};
+      engine::check(sb_filter_eval(engine.handle, local_partition, plan.nodes.data(), static_cast<uint32_t>(plan.nodes.size()), &filters.results[0]));
+      size_t size = 0;
+      engine::check(sb_result_export_portable(filters.results[0], nullptr, 0, &size));
+      *bytes = static_cast<uint8_t*>(malloc(std::max<size_t>(1, size)));
+      engine::check(sb_result_export_portable(filters.results[0], *bytes, size, n));
+   });
+}
+// Test hook: the ids held by CRoaring portable bytes, read with the host's restated reader (host/roaring.hpp readPortable)
+int silo_portable_ids(const uint8_t* bytes, size_t n_bytes, uint32_t** ids, size_t* n) {
+   return capi::guarded([&] {
+      size_t consumed = 0;
+      const Bitmap bitmap = Bitmap::readPortable(bytes, n_bytes, &consumed);
+      if (consumed != n_bytes) throw std::runtime_error("portable bytes: " + std::to_string(n_bytes - consumed) + " bytes left over");
+      const std::vector<uint32_t> values = bitmap.toVector();
+      *ids = static_cast<uint32_t*>(malloc(std::max<size_t>(1, values.size()) * sizeof(uint32_t)));
+      memcpy(*ids, values.data(), values.size() * sizeof(uint32_t));
+      *n = values.size();
+   });
+}
+
 // Operator known-answer tests: a literal operator tree evaluated on the GPU.
 int silo_engine_eval_optree(int device, const char* optree_json, uint32_t** ids, size_t* n) {
    return capi::guarded([&] {

@@ -79,6 +79,8 @@ def host():
         "silo_engine_execute_partial": (vp, [vp, cp]),
         "silo_merge_partials": (vp, [vp, cp, ctypes.POINTER(cp), u32]),
         "silo_alias_apply": (vp, [cp, cp, ctypes.c_int]),
+        "silo_engine_filter_portable": (ctypes.c_int, [vp, cp, u32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
+        "silo_portable_ids": (ctypes.c_int, [cp, ctypes.c_size_t, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32, u32]),
         "silo_synth_owned_count": (u32, [vp]),
         "silo_synth_owned": (u32, [vp, u32]),
@@ -346,6 +348,17 @@ class Engine:
             raise _error()
         return _take_ids(ptr, n.value)
 
+    def filter_portable(self, filter_expression, local_partition):
+        """the filter's rows as CRoaring portable bytes (sb_result_export_portable)"""
+        f = filter_expression if isinstance(filter_expression, str) else json.dumps(filter_expression)
+        ptr, n = ctypes.c_void_p(), ctypes.c_size_t()
+        if host().silo_engine_filter_portable(self.handle, f.encode(), local_partition, ctypes.byref(ptr), ctypes.byref(n)) != 0:
+            raise _error()
+        try:
+            return ctypes.string_at(ptr, n.value)
+        finally:
+            host().silo_free(ptr)
+
     def close(self):
         if self.handle:
             host().silo_engine_free(self.handle)
@@ -505,6 +518,14 @@ def merge_partials(db, query, partial_texts):
 def alias_apply(alias_map, lineage, alias=False):
     """host PangoLineageAliasLookup (storage.hpp) built from {alias: [values]}: unalias(lineage), or alias(lineage) with alias=True"""
     return _take_string(host().silo_alias_apply(json.dumps(alias_map).encode(), lineage.encode(), 1 if alias else 0))
+
+
+def portable_ids(data):
+    """the ids in CRoaring portable bytes, read by the host's restated reader (host/roaring.hpp)"""
+    ptr, n = ctypes.c_void_p(), ctypes.c_size_t()
+    if host().silo_portable_ids(data, len(data), ctypes.byref(ptr), ctypes.byref(n)) != 0:
+        raise _error()
+    return _take_ids(ptr, n.value)
 
 
 def run_many(engine, prepared):
