@@ -123,3 +123,55 @@ def test_the_device_answers_and_refuses_as_the_oracle_does(libs, example_db):
         assert answered > 400 and nonempty > 150
     finally:
         engine.close()
+
+
+def thousand_leaf(rng):
+    return rng.choice([
+        {"type": "NucleotideEquals", "position": rng.randint(1, 29903), "symbol": rng.choice("ACGTN-")},
+        {"type": "NucleotideEquals", "position": rng.choice([241, 3037, 14408, 23403, 28881]), "symbol": rng.choice("ACGT")},
+        {"type": "AminoAcidEquals", "sequenceName": rng.choice(["S", "N", "ORF1a"]), "position": rng.randint(1, 400), "symbol": rng.choice("ADGLX.")},
+        {"type": "HasNucleotideMutation", "position": rng.choice([241, 3037, 14408, 23403, rng.randint(1, 29903)])},
+        {"type": "HasAminoAcidMutation", "sequenceName": "S", "position": rng.choice([222, 501, 614, 681])},
+        {"type": "PangoLineage", "column": "pangoLineage", "value": rng.choice(["D.2", "A.2.2", "B.1", "B", "B.1.1.7"]), "includeSublineages": rng.random() < 0.5},
+        {"type": "DateBetween", "column": "date", "from": rng.choice([None, "2020-06-01", "2021-01-01"]), "to": rng.choice([None, "2020-12-31", "2021-06-30"])},
+        {"type": "IntBetween", "column": "age", "from": rng.choice([None, 20]), "to": rng.choice([None, 60])},
+        {"type": "FloatBetween", "column": "nextcladeQcOverallScore", "from": rng.choice([None, 1.0]), "to": rng.choice([None, 50.0])},
+        {"type": "StringEquals", "column": rng.choice(["country", "region", "division"]), "value": rng.choice(["Australia", "Oceania", "Victoria", "Europe", ""])},
+    ])
+
+
+@pytest.mark.gpu
+def test_random_queries_on_the_thousand_sequence_dataset(libs, thousand_db):
+    """BASELINE config C1's dataset (real sequences: run containers, 11 lineage partitions, rows ordered by date): 250 random trees
+    under every action of the path, device == oracle in its reference-shaped (faithful) mode"""
+    pysilo, oracle = libs
+    rng = random.Random(2024)
+    actions = [{"type": "Aggregated"}, {"type": "Mutations", "minProportion": 0.05}, {"type": "Mutations", "minProportion": 0.0},
+               {"type": "AminoAcidMutations", "minProportion": 0.05, "sequenceName": "S"}, {"type": "AminoAcidMutations", "minProportion": 0.2},
+               {"type": "Aggregated", "groupByFields": ["pangoLineage", "country"], "orderByFields": ["pangoLineage", "country"]},
+               {"type": "Aggregated", "groupByFields": ["date"], "orderByFields": [{"field": "count", "order": "descending"}, "date"], "limit": 10}]
+
+    def random_tree(depth):
+        if depth == 0 or rng.random() < 0.3:
+            return thousand_leaf(rng)
+        kind = rng.randrange(5)
+        if kind <= 1:
+            return {"type": ("And", "Or")[kind], "children": [random_tree(depth - 1) for _ in range(rng.randint(1, 3))]}
+        if kind == 2:
+            return {"type": "Not", "child": random_tree(depth - 1)}
+        if kind == 3:
+            return {"type": rng.choice(["Maybe", "Exact"]), "child": random_tree(depth - 1)}
+        children = [random_tree(depth - 1) for _ in range(rng.randint(1, 4))]
+        return {"type": "N-Of", "numberOfMatchers": rng.randint(0, len(children)), "matchExactly": rng.random() < 0.5, "children": children}
+    engine = pysilo.Engine(thousand_db, 0)
+    try:
+        nonempty = 0
+        for k in range(250):
+            query = {"action": actions[k % len(actions)], "filterExpression": random_tree(3)}
+            want = answer(lambda q: oracle.execute(thousand_db, q), query)
+            got = answer(engine.execute, query)
+            assert got == want, json.dumps(query)
+            nonempty += want[0] == "ok" and len(want[1]) > 0 and want[1] != [{"count": 0}]
+        assert nonempty > 100
+    finally:
+        engine.close()
