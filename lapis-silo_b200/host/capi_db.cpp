@@ -62,6 +62,21 @@ char* silo_alias_apply(const char* alias_json, const char* lineage, int directio
    });
    return out;
 }
+// Test hook (tests/test_host_cpu.py): the entries of a FASTA text as the builder reads them, as a JSON array of [key, sequence]
+char* silo_parse_fasta(const char* text, size_t n) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      json::Value entries = json::Value::array();
+      for (const auto& [key, genome] : io::readFastaEntries(std::string(text, n))) {
+         json::Value entry = json::Value::array();
+         entry.arr.push_back(json::Value::string(key));
+         entry.arr.push_back(json::Value::string(genome));
+         entries.arr.push_back(std::move(entry));
+      }
+      out = capi::dupString(entries.dump());
+   });
+   return out;
+}
 void silo_db_free(void* db) { delete static_cast<Database*>(db); }
 uint32_t silo_db_partition_count(const void* db) { return static_cast<uint32_t>(static_cast<const Database*>(db)->partitions.size()); }
 uint32_t silo_db_partition_rows(const void* db, uint32_t p) { return static_cast<const Database*>(db)->partitions.at(p)->sequence_count; }

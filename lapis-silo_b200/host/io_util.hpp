@@ -64,21 +64,33 @@ inline std::string readMaybeCompressed(const std::string& base, bool& found) {
    return "";
 }
 
-inline std::map<std::string, std::string> parseFasta(const std::string& text) {
-   std::map<std::string, std::string> out;
+// common/fasta_reader.cpp:13-46 (FastaReader::nextKey / next): one line with the key after '>', one line with the whole sequence, and
+// so on; a key line without '>' (an empty line included) and a key without a following line are FastaFormatExceptions with the
+// reference's texts. Lines are what getline yields: split at '\n', nothing trimmed.
+struct FastaFormatException : std::runtime_error { using std::runtime_error::runtime_error; };
+inline std::vector<std::pair<std::string, std::string>> readFastaEntries(const std::string& text) {
+   std::vector<std::pair<std::string, std::string>> out;
    size_t pos = 0;
-   std::string key;
-   while (pos < text.size()) {
+   auto getline = [&](std::string& line) {      // std::getline on a stream holding `text`
+      if (pos >= text.size()) return false;
       size_t eol = text.find('\n', pos);
       if (eol == std::string::npos) eol = text.size();
-      size_t len = eol - pos;
-      if (len && text[pos + len - 1] == '\r') --len;
-      if (len) {
-         if (text[pos] == '>') { key = text.substr(pos + 1, len - 1); out[key]; }
-         else out[key].append(text, pos, len);
-      }
+      line.assign(text, pos, eol - pos);
       pos = eol + 1;
+      return true;
+   };
+   std::string key_with_prefix, genome;
+   while (getline(key_with_prefix)) {
+      if (key_with_prefix.empty() || key_with_prefix[0] != '>') throw FastaFormatException("Fasta key prefix '>' missing for key: " + key_with_prefix);
+      std::string key = key_with_prefix.substr(1);
+      if (!getline(genome)) throw FastaFormatException("Missing genome sequence in line following key: " + key);
+      out.emplace_back(std::move(key), genome);
    }
+   return out;
+}
+inline std::map<std::string, std::string> parseFasta(const std::string& text) {
+   std::map<std::string, std::string> out;
+   for (auto& [key, genome] : readFastaEntries(text)) out[key] = std::move(genome);
    return out;
 }
 

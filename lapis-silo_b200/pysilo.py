@@ -79,6 +79,7 @@ def host():
         "silo_engine_execute_partial": (vp, [vp, cp]),
         "silo_merge_partials": (vp, [vp, cp, ctypes.POINTER(cp), u32]),
         "silo_alias_apply": (vp, [cp, cp, ctypes.c_int]),
+        "silo_parse_fasta": (vp, [cp, ctypes.c_size_t]),
         "silo_engine_filter_portable": (ctypes.c_int, [vp, cp, u32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
         "silo_portable_ids": (ctypes.c_int, [cp, ctypes.c_size_t, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32, u32]),
@@ -518,6 +519,12 @@ def merge_partials(db, query, partial_texts):
 def alias_apply(alias_map, lineage, alias=False):
     """host PangoLineageAliasLookup (storage.hpp) built from {alias: [values]}: unalias(lineage), or alias(lineage) with alias=True"""
     return _take_string(host().silo_alias_apply(json.dumps(alias_map).encode(), lineage.encode(), 1 if alias else 0))
+
+
+def parse_fasta(text):
+    """[key, sequence] pairs of a FASTA text as the builder reads it (host/io_util.hpp readFastaEntries)"""
+    data = text if isinstance(text, bytes) else text.encode()
+    return json.loads(_take_string(host().silo_parse_fasta(data, len(data))))
 
 
 def portable_ids(data):

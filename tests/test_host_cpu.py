@@ -173,3 +173,22 @@ def test_query_error_messages_are_the_reference_s(libs, example_db):
         if "regex" not in m["text"]:
             assert err.value.message == m["text"]
     assert literal >= 90
+
+
+def test_fasta_reader_on_the_reference_s_files(libs):
+    """common/fasta_reader.test.cpp:9-84 on copies of its four input files: two entries; no newline at the end; a first line without '>';
+    a key without a sequence line -- the last two are FastaFormatExceptions with the reference's texts (fasta_reader.cpp:19-21,41-43)"""
+    from pathlib import Path
+    pysilo, _ = libs
+    files = Path(__file__).parent / "golden" / "fastaFiles"
+    assert pysilo.parse_fasta((files / "test.fasta").read_bytes()) == [["Key1", "ACGT"], ["Key2", "CGTA"]]
+    assert pysilo.parse_fasta((files / "no_end_new_line.fasta").read_bytes()) == [["Key", "ACGT"]]
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.parse_fasta((files / "wrong_format.fasta").read_bytes())
+    assert "Fasta key prefix '>' missing for key: ACGT" in str(err.value)
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.parse_fasta((files / "missing_genome.fasta").read_bytes())
+    assert "Missing genome sequence in line following key: Key_without_genome" in str(err.value)
+    assert pysilo.parse_fasta(b"") == [] and pysilo.parse_fasta(b">k\n\n") == [["k", ""]]
+    with pytest.raises(pysilo.SiloError):
+        pysilo.parse_fasta(b">k\nACGT\n\n")      # an empty line where a key is expected
