@@ -192,3 +192,32 @@ def test_fasta_reader_on_the_reference_s_files(libs):
     assert pysilo.parse_fasta(b"") == [] and pysilo.parse_fasta(b">k\n\n") == [["k", ""]]
     with pytest.raises(pysilo.SiloError):
         pysilo.parse_fasta(b">k\nACGT\n\n")      # an empty line where a key is expected
+
+
+def test_reference_genomes_as_the_reference_reads_them(libs, example_db):
+    """storage/reference_genomes.test.cpp:8-32, asked through the query path: the '.' symbol of AminoAcidEquals is the reference symbol
+    (aa_symbol_equals.cpp:53-54) and NucleotideEquals / AminoAcidEquals refuse a position beyond the reference with its length in the text"""
+    _, oracle = libs
+    info = example_db.info()["sequences"]
+    assert len([n for n in info if n in ("main", "testSecondSequence")]) == 2
+    nuc = lambda name, pos, sym: {"type": "NucleotideEquals", "sequenceName": name, "position": pos, "symbol": sym}
+    aa = lambda name, pos, sym: {"type": "AminoAcidEquals", "sequenceName": name, "position": pos, "symbol": sym}
+    count = lambda flt: oracle.execute(example_db, {"action": {"type": "Aggregated"}, "filterExpression": flt})[0]["count"]
+    for name, length, index, symbol in (("S", 1274, 3, "F"), ("ORF1a", 4401, 10, "K"), ("ORF9b", 98, 10, "A")):
+        assert count(aa(name, index + 1, ".")) == count(aa(name, index + 1, symbol)) > 0
+        for other in "ACDEFGHIKLMNPQRSTVWY":
+            if other != symbol:
+                assert count({"type": "And", "children": [aa(name, index + 1, "."), aa(name, index + 1, other)]}) == 0
+        count(aa(name, length, "X"))      # the last position is there (its reference symbol is the stop codon: quirk Q4 forbids '.')
+        with pytest.raises(oracle.OracleError) as err:
+            count(aa(name, length + 1, "."))
+        assert err.value.kind == "parse" and err.value.message == f"AminoAcidEquals position is out of bounds '{length + 1}' > '{length}'"
+    for name, length, index, symbol in (("main", 29903, 0, "A"), ("testSecondSequence", 4, 1, "C")):
+        # most rows carry the reference base: Mutations never reports it, and HasNucleotideMutation is the complement of it among A, C, G, T
+        rows = oracle.execute(example_db, {"action": {"type": "Mutations", "sequenceName": name, "minProportion": 0.0}, "filterExpression": {"type": "True"}})
+        assert all(r["mutation"][0] == symbol for r in rows if r["mutation"][1:-1] == str(index + 1))
+        assert not any(r["mutation"] == f"{symbol}{index + 1}{symbol}" for r in rows)
+        count(nuc(name, length, "A"))
+        with pytest.raises(oracle.OracleError) as err:
+            count(nuc(name, length + 1, "A"))
+        assert err.value.kind == "parse" and err.value.message == f"NucleotideEquals position is out of bounds '{length + 1}' > '{length}'"
