@@ -108,14 +108,17 @@ inline ColumnType columnTypeFromConfig(const std::string& type, bool generate_in
 inline DatabaseConfig parseDatabaseConfig(const std::string& text) {  // config/database_config.cpp:60-130
    DatabaseConfig config;
    std::string cur_name, cur_type;
-   bool cur_index = false, cur_index_set = false, in_item = false;
+   bool cur_index = false, cur_index_set = false, in_item = false, has_metadata = false;
    auto flush = [&] {
       if (!in_item) return;
       bool gen = cur_index_set ? cur_index : cur_type == "pango_lineage";
       config.metadata.push_back({cur_name, columnTypeFromConfig(cur_type, gen, cur_name)});
       in_item = false; cur_index_set = false; cur_index = false;
    };
+   bool in_metadata = false;      // list items belong to the key above them: only those under `metadata` are columns
    for (const auto& y : io::parseYamlLines(text)) {
+      if (!y.list_item && y.indent < 4) { flush(); in_metadata = y.key == "metadata"; }
+      if (!in_metadata && (y.list_item || y.indent >= 4)) continue;
       if (y.list_item) { flush(); in_item = true; }
       if (in_item && y.indent >= 4) {
          if (y.key == "name") cur_name = y.value;
@@ -124,6 +127,7 @@ inline DatabaseConfig parseDatabaseConfig(const std::string& text) {  // config/
          continue;
       }
       flush();
+      if (y.key == "metadata") has_metadata = true;
       if (y.key == "instanceName") config.instance_name = y.value;
       else if (y.key == "primaryKey") config.primary_key = y.value;
       else if (y.key == "dateToSortBy") config.date_to_sort_by = y.value;
@@ -131,6 +135,8 @@ inline DatabaseConfig parseDatabaseConfig(const std::string& text) {  // config/
       else if (y.key == "defaultNucleotideSequence") config.default_nucleotide_sequence = y.value;
    }
    flush();
+   // yaml-cpp's text when schema["metadata"] is dereferenced and absent (database_config.test.cpp:149-160)
+   if (!has_metadata) throw std::runtime_error("invalid node; first invalid key: \"metadata\"");
    return config;
 }
 

@@ -77,6 +77,29 @@ char* silo_parse_fasta(const char* text, size_t n) {
    });
    return out;
 }
+// Test hook (tests/test_host_cpu.py): a database_config.yaml text as the builder understands it
+char* silo_parse_database_config(const char* text) {
+   char* out = nullptr;
+   capi::guarded([&] {
+      static const char* const names[] = {"STRING", "INDEXED_STRING", "INDEXED_PANGOLINEAGE", "DATE", "INT", "FLOAT", "NUC_INSERTION", "AA_INSERTION"};
+      const DatabaseConfig config = builder::parseDatabaseConfig(text);
+      json::Value j = json::Value::object();
+      j.set("instanceName", json::Value::string(config.instance_name));
+      j.set("primaryKey", json::Value::string(config.primary_key));
+      j.set("dateToSortBy", config.date_to_sort_by ? json::Value::string(*config.date_to_sort_by) : json::Value::null());
+      j.set("partitionBy", config.partition_by ? json::Value::string(*config.partition_by) : json::Value::null());
+      json::Value metadata = json::Value::array();
+      for (const auto& m : config.metadata) {
+         json::Value entry = json::Value::array();
+         entry.arr.push_back(json::Value::string(m.name));
+         entry.arr.push_back(json::Value::string(names[static_cast<int>(m.type)]));
+         metadata.arr.push_back(std::move(entry));
+      }
+      j.set("metadata", std::move(metadata));
+      out = capi::dupString(j.dump());
+   });
+   return out;
+}
 void silo_db_free(void* db) { delete static_cast<Database*>(db); }
 uint32_t silo_db_partition_count(const void* db) { return static_cast<uint32_t>(static_cast<const Database*>(db)->partitions.size()); }
 uint32_t silo_db_partition_rows(const void* db, uint32_t p) { return static_cast<const Database*>(db)->partitions.at(p)->sequence_count; }

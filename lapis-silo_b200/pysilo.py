@@ -80,6 +80,7 @@ def host():
         "silo_merge_partials": (vp, [vp, cp, ctypes.POINTER(cp), u32]),
         "silo_alias_apply": (vp, [cp, cp, ctypes.c_int]),
         "silo_parse_fasta": (vp, [cp, ctypes.c_size_t]),
+        "silo_parse_database_config": (vp, [cp]),
         "silo_engine_filter_portable": (ctypes.c_int, [vp, cp, u32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
         "silo_portable_ids": (ctypes.c_int, [cp, ctypes.c_size_t, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]),
         "silo_synth_generate": (vp, [cp, u64, u64, ctypes.c_int, ctypes.c_int, u32, u32, u32, u32, u32]),
@@ -525,6 +526,11 @@ def parse_fasta(text):
     """[key, sequence] pairs of a FASTA text as the builder reads it (host/io_util.hpp readFastaEntries)"""
     data = text if isinstance(text, bytes) else text.encode()
     return json.loads(_take_string(host().silo_parse_fasta(data, len(data))))
+
+
+def parse_database_config(text):
+    """a database_config.yaml text as the builder understands it (host/builder.hpp parseDatabaseConfig)"""
+    return json.loads(_take_string(host().silo_parse_database_config(text.encode() if isinstance(text, str) else text)))
 
 
 def portable_ids(data):

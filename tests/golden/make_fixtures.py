@@ -3,6 +3,7 @@
 Copies DATA, never source code:
   * exampleDataset/            the reference's 100-sequence test dataset inputs (testBaseData/exampleDataset)
   * exampleDataset1000Sequences/  BASELINE config C1 inputs
+  * configs/                    the database_config files of config/database_config.test.cpp
   * fastaFiles/                 the four inputs of common/fasta_reader.test.cpp (and their .zstdfasta twins)
   * fastaFilesWithMissingSequences/, ndjsonWithNullSequences/, ndjsonWithSqlKeywordField/, tsvWithSqlKeywordField/
                                the four tiny input directories of preprocessing/preprocessor.test.cpp (whole directories)
@@ -42,6 +43,9 @@ def main():
         dst.mkdir(exist_ok=True)
         for f in sorted((REF / "testBaseData" / name).iterdir()):
             shutil.copyfile(f, dst / f.name)
+    (OUT / "configs").mkdir(exist_ok=True)
+    for f in sorted((REF / "testBaseData").glob("test_database_config*.yaml")):      # config/database_config.test.cpp
+        shutil.copyfile(f, OUT / "configs" / f.name)
     skipped = []
     for sub in ["queries", "invalidQueries"]:
         dst = OUT / sub

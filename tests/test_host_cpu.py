@@ -221,3 +221,34 @@ def test_reference_genomes_as_the_reference_reads_them(libs, example_db):
         with pytest.raises(oracle.OracleError) as err:
             count(nuc(name, length + 1, "A"))
         assert err.value.kind == "parse" and err.value.message == f"NucleotideEquals position is out of bounds '{length + 1}' > '{length}'"
+
+
+def test_database_config_reader_on_the_reference_s_files(libs):
+    """config/database_config.test.cpp:52-176 on copies of its yaml files: column types per (type, generateIndex), the full test config,
+    optional dateToSortBy / partitionBy, additional entries ignored, an unknown type and a missing metadata node refused"""
+    from pathlib import Path
+    pysilo, _ = libs
+    configs = Path(__file__).parent / "golden" / "configs"
+    read = lambda name: pysilo.parse_database_config((configs / name).read_text())
+    config = read("test_database_config.yaml")
+    assert config["instanceName"] == "sars_cov-2_minimal_test_config" and config["primaryKey"] == "gisaid_epi_isl"
+    assert config["dateToSortBy"] == "date" and config["partitionBy"] == "pango_lineage"
+    assert config["metadata"] == [["gisaid_epi_isl", "STRING"], ["date", "DATE"], ["unsorted_date", "DATE"], ["region", "INDEXED_STRING"], ["country", "INDEXED_STRING"],
+                                  ["pango_lineage", "INDEXED_PANGOLINEAGE"], ["division", "INDEXED_STRING"], ["age", "INT"], ["qc_value", "FLOAT"],
+                                  ["nucleotideInsertions", "NUC_INSERTION"], ["aminoAcidInsertions", "AA_INSERTION"]]
+    assert read("test_database_config_without_date_to_sort_by.yaml")["dateToSortBy"] is None
+    without_partition = read("test_database_config_without_partition_by.yaml")
+    assert without_partition["partitionBy"] is None and without_partition["dateToSortBy"] == "date" and len(without_partition["metadata"]) == 10
+    additional = read("test_database_config_with_additional_entries.yaml")
+    assert [m[0] for m in additional["metadata"]] == ["gisaid_epi_isl", "date", "region", "country", "pangoLineage"]
+    with pytest.raises(pysilo.SiloError) as err:
+        read("test_database_config_with_invalid_metadata_type.yaml")
+    assert "wrong_type" in str(err.value)
+    with pytest.raises(pysilo.SiloError) as err:
+        read("test_database_config_with_invalid_structure.yaml")
+    assert 'invalid node; first invalid key: "metadata"' in str(err.value)
+    # database_config.test.cpp:64-75: the column type of every (value type, generateIndex) pair
+    typed = lambda kind, index: pysilo.parse_database_config(
+        f"schema:\n  instanceName: x\n  metadata:\n    - name: testName\n      type: {kind}\n" + ("      generateIndex: true\n" if index else "") + "  primaryKey: testName\n")["metadata"][0][1]
+    assert [typed("string", False), typed("string", True), typed("date", False), typed("pango_lineage", True), typed("int", False), typed("float", False),
+            typed("insertion", False), typed("aaInsertion", False)] == ["STRING", "INDEXED_STRING", "DATE", "INDEXED_PANGOLINEAGE", "INT", "FLOAT", "NUC_INSERTION", "AA_INSERTION"]
