@@ -277,6 +277,12 @@ inline PangoLineageAliasLookup readAliasFile(const std::string& path) {
    return lookup;
 }
 
+// preprocessing/metadata_info.cpp:39-46: every metadata field of the database config has to be in the input (the header of the
+// metadata file; for ndjson the keys of the FIRST record's "metadata" object, :129-160)
+inline void requireMetadataField(const std::string& name, bool present) {
+   if (!present) throw std::runtime_error("The metadata field '" + name + "' which is contained in the database config is not contained in the input.");
+}
+
 inline std::string jsonScalarToString(const json::Value& v) {
    if (v.is_string()) return v.s;
    if (v.is_boolean()) return v.b ? "true" : "false";
@@ -308,6 +314,8 @@ inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& d
          if (eol == std::string::npos) eol = text.size();
          if (eol > pos) {
             json::Value j = json::parse(text.data() + pos, eol - pos);
+            if (records.empty()) for (const auto& m : config.metadata)      // the two insertion lists live beside "metadata" (metadata_info.cpp:61-95)
+               requireMetadataField(m.name, j["metadata"].contains(m.name) || ((m.name == "nucleotideInsertions" || m.name == "aminoAcidInsertions") && j.contains(m.name)));
             InputRecord rec;
             for (const auto& [k, v] : j["metadata"].obj) rec.metadata[k] = v.is_null() ? std::nullopt : std::optional<std::string>(jsonScalarToString(v));
             for (const auto& [k, v] : j["alignedNucleotideSequences"].obj) rec.nuc_sequences[k] = v.is_null() ? std::nullopt : std::optional<std::string>(v.s);
@@ -325,6 +333,7 @@ inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& d
       }
    } else {
       io::Table table = io::parseTsv(io::readFile(dir + "/" + metadata_file));
+      for (const auto& m : config.metadata) requireMetadataField(m.name, table.columnIndex(m.name) >= 0);
       const int pk = table.columnIndex(config.primary_key);
       if (pk < 0) throw std::runtime_error("metadata file has no primary key column " + config.primary_key);
       std::map<std::string, std::map<std::string, std::string>> nuc_fasta, aa_fasta;

@@ -252,3 +252,30 @@ def test_database_config_reader_on_the_reference_s_files(libs):
         f"schema:\n  instanceName: x\n  metadata:\n    - name: testName\n      type: {kind}\n" + ("      generateIndex: true\n" if index else "") + "  primaryKey: testName\n")["metadata"][0][1]
     assert [typed("string", False), typed("string", True), typed("date", False), typed("pango_lineage", True), typed("int", False), typed("float", False),
             typed("insertion", False), typed("aaInsertion", False)] == ["STRING", "INDEXED_STRING", "DATE", "INDEXED_PANGOLINEAGE", "INT", "FLOAT", "NUC_INSERTION", "AA_INSERTION"]
+
+
+def test_metadata_fields_of_the_config_must_be_in_the_input(libs, tmp_path):
+    """preprocessing/metadata_info.test.cpp:8-31 (and :39-46 of metadata_info.cpp): a column of the database config that the metadata
+    file (or the first ndjson record) does not have stops the build with the reference's text; the valid configs of :33-83 build"""
+    import json
+    import shutil
+    from pathlib import Path
+    pysilo, _ = libs
+    golden = Path(__file__).parent / "golden"
+
+    def directory(name, source, schema_columns, tail):
+        d = tmp_path / name
+        shutil.copytree(golden / source, d)
+        (d / "database_config.yaml").write_text("schema:\n  instanceName: testInstanceName\n  metadata:\n" +
+                                                "".join(f"    - name: {n}\n      type: {t}\n" for n, t in schema_columns) + tail)
+        return d
+    bad = [("gisaid_epi_isl", "string"), ("notInMetadata", "pango_lineage"), ("country", "string")]
+    good = [("gisaid_epi_isl", "string"), ("pango_lineage", "pango_lineage"), ("date", "date"), ("country", "string")]
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.Database.from_directory(directory("bad_tsv", "exampleDataset", bad, "  primaryKey: gisaid_epi_isl\n"))
+    assert "The metadata field 'notInMetadata' which is contained in the database config is not contained in the input." in str(err.value)
+    db = pysilo.Database.from_directory(directory("good_tsv", "exampleDataset", good, "  primaryKey: gisaid_epi_isl\n"))
+    assert db.info()["sequenceCount"] == 100
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.Database.from_directory(directory("bad_ndjson", "ndjsonWithSqlKeywordField", [("primaryKey", "string"), ("group", "string"), ("absent", "int")], "  primaryKey: primaryKey\n"))
+    assert "The metadata field 'absent' which is contained in the database config is not contained in the input." in str(err.value)
