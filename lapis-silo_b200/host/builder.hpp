@@ -283,6 +283,15 @@ inline void requireMetadataField(const std::string& name, bool present) {
    if (!present) throw std::runtime_error("The metadata field '" + name + "' which is contained in the database config is not contained in the input.");
 }
 
+// preprocessing/sequence_info.cpp:79-151: the sequence names of the FIRST ndjson record and of the reference genomes must be the same
+// sets, both ways, for nucleotide sequences and for genes
+inline void validateSequenceNames(const json::Value& in_record, const std::map<std::string, std::string>& references, const char* what, const std::string& file) {
+   for (const auto& [name, _] : in_record.obj)
+      if (!references.count(name)) throw std::runtime_error(std::string("The aligned ") + what + " sequence " + name + " which is contained in the input file " + file + " is not contained in the reference sequences.");
+   for (const auto& [name, _] : references)
+      if (!in_record.contains(name)) throw std::runtime_error(std::string("The aligned ") + what + " sequence " + name + " which is contained in the reference sequences is not contained in the input file " + file + ".");
+}
+
 inline std::string jsonScalarToString(const json::Value& v) {
    if (v.is_string()) return v.s;
    if (v.is_boolean()) return v.b ? "true" : "false";
@@ -308,14 +317,29 @@ inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& d
    if (!ndjson_file.empty()) {
       std::string text = io::readFile(dir + "/" + ndjson_file);
       if (ndjson_file.size() > 4 && ndjson_file.substr(ndjson_file.size() - 4) == ".zst") text = io::zstdDecompress(text);
-      size_t pos = 0;
-      while (pos < text.size()) {
-         size_t eol = text.find('\n', pos);
-         if (eol == std::string::npos) eol = text.size();
-         if (eol > pos) {
-            json::Value j = json::parse(text.data() + pos, eol - pos);
+      // one record per line; a file whose first line only opens an object is one pretty-printed record (DuckDB's read_json, which the
+      // reference reads its input with, detects both layouts: testBaseData/ndjsonFiles/oneline_*.json)
+      std::vector<std::pair<size_t, size_t>> documents;      // {offset, length}
+      const size_t first_eol = std::min(text.find('\n'), text.size());
+      const size_t first_end = text.find_last_not_of(" \t\r", first_eol == 0 ? 0 : first_eol - 1);
+      if (first_eol > 0 && first_end != std::string::npos && first_end < first_eol && text.find_first_not_of(" \t") == first_end && text[first_end] == '{') documents.emplace_back(0, text.size());
+      else {
+         for (size_t pos = 0; pos < text.size();) {
+            size_t eol = text.find('\n', pos);
+            if (eol == std::string::npos) eol = text.size();
+            if (eol > pos) documents.emplace_back(pos, eol - pos);
+            pos = eol + 1;
+         }
+      }
+      for (const auto& [offset, length] : documents) {
+         {
+            json::Value j = json::parse(text.data() + offset, length);
             if (records.empty()) for (const auto& m : config.metadata)      // the two insertion lists live beside "metadata" (metadata_info.cpp:61-95)
                requireMetadataField(m.name, j["metadata"].contains(m.name) || ((m.name == "nucleotideInsertions" || m.name == "aminoAcidInsertions") && j.contains(m.name)));
+            if (records.empty()) {
+               validateSequenceNames(j["alignedNucleotideSequences"], nuc_refs, "nucleotide", dir + "/" + ndjson_file);
+               validateSequenceNames(j["alignedAminoAcidSequences"], aa_refs, "amino acid", dir + "/" + ndjson_file);
+            }
             InputRecord rec;
             for (const auto& [k, v] : j["metadata"].obj) rec.metadata[k] = v.is_null() ? std::nullopt : std::optional<std::string>(jsonScalarToString(v));
             for (const auto& [k, v] : j["alignedNucleotideSequences"].obj) rec.nuc_sequences[k] = v.is_null() ? std::nullopt : std::optional<std::string>(v.s);
@@ -329,7 +353,6 @@ inline std::unique_ptr<Database> buildDatabaseFromDirectory(const std::string& d
             }
             records.push_back(std::move(rec));
          }
-         pos = eol + 1;
       }
    } else {
       io::Table table = io::parseTsv(io::readFile(dir + "/" + metadata_file));

@@ -4,6 +4,7 @@ Copies DATA, never source code:
   * exampleDataset/            the reference's 100-sequence test dataset inputs (testBaseData/exampleDataset)
   * exampleDataset1000Sequences/  BASELINE config C1 inputs
   * configs/                    the database_config files of config/database_config.test.cpp
+  * ndjsonFiles/                the inputs of preprocessing/sequence_info.test.cpp
   * fastaFiles/                 the four inputs of common/fasta_reader.test.cpp (and their .zstdfasta twins)
   * fastaFilesWithMissingSequences/, ndjsonWithNullSequences/, ndjsonWithSqlKeywordField/, tsvWithSqlKeywordField/
                                the four tiny input directories of preprocessing/preprocessor.test.cpp (whole directories)
@@ -28,7 +29,7 @@ DATASET_FILES = {
         "database_config.yaml", "preprocessing_config.yaml", "reference_genomes.json", "pangolineage_alias.json", "sample.ndjson.zst",
     ],
 }
-WHOLE_DATASETS = ["fastaFiles", "fastaFilesWithMissingSequences", "ndjsonWithNullSequences", "ndjsonWithSqlKeywordField", "tsvWithSqlKeywordField"]
+WHOLE_DATASETS = ["ndjsonFiles", "fastaFiles", "fastaFilesWithMissingSequences", "ndjsonWithNullSequences", "ndjsonWithSqlKeywordField", "tsvWithSqlKeywordField"]
 HOT_ACTIONS = {"Mutations", "AminoAcidMutations", "Aggregated"}
 
 

@@ -279,3 +279,51 @@ def test_metadata_fields_of_the_config_must_be_in_the_input(libs, tmp_path):
     with pytest.raises(pysilo.SiloError) as err:
         pysilo.Database.from_directory(directory("bad_ndjson", "ndjsonWithSqlKeywordField", [("primaryKey", "string"), ("group", "string"), ("absent", "int")], "  primaryKey: primaryKey\n"))
     assert "The metadata field 'absent' which is contained in the database config is not contained in the input." in str(err.value)
+
+
+def test_sequence_names_of_the_input_must_be_those_of_the_reference_genomes(libs, tmp_path):
+    """preprocessing/sequence_info.test.cpp:12-65 on copies of its inputs: the 1,000-sequence ndjson validates against its own reference
+    genomes; it fails against exampleDataset's (a second nucleotide sequence the input lacks); an input with a second nucleotide sequence
+    or without the ORF genes fails against the 1,000-sequence references -- with the texts of sequence_info.cpp:107-150"""
+    import shutil
+    from pathlib import Path
+    pysilo, _ = libs
+    golden = Path(__file__).parent / "golden"
+    thousand = golden / "exampleDataset1000Sequences"
+
+    def directory(name, ndjson, references):
+        d = tmp_path / name
+        d.mkdir()
+        for f in ("database_config.yaml", "pangolineage_alias.json"):
+            shutil.copyfile(thousand / f, d / f)
+        shutil.copyfile(ndjson, d / ndjson.name)
+        shutil.copyfile(references, d / "reference_genomes.json")
+        (d / "preprocessing_config.yaml").write_text(f'ndjsonInputFilename: "{ndjson.name}"\npangoLineageDefinitionFilename: "pangolineage_alias.json"\nreferenceGenomeFilename: "reference_genomes.json"\n')
+        return d
+    ok = pysilo.Database.from_directory(directory("ok", thousand / "sample.ndjson.zst", thousand / "reference_genomes.json"))
+    assert ok.info()["sequenceCount"] == 1000
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.Database.from_directory(directory("too_many_references", thousand / "sample.ndjson.zst", golden / "exampleDataset" / "reference_genomes.json"))
+    assert "The aligned nucleotide sequence testSecondSequence which is contained in the reference sequences is not contained in the input file" in str(err.value)
+    # oneline_second_nuc.json is not valid JSON (no comma before its second nucleotide sequence): refused by the parser here, by DuckDB's
+    # in the reference (sequence_info.cpp:86-92); with the comma put in, the name check refuses it
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.Database.from_directory(directory("too_many_in_json", golden / "ndjsonFiles" / "oneline_second_nuc.json.zst", thousand / "reference_genomes.json"))
+    assert "JSON" in str(err.value)
+    import ctypes
+    zstd = ctypes.CDLL("libzstd.so.1")
+    zstd.ZSTD_decompress.restype = ctypes.c_size_t
+    zstd.ZSTD_decompress.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t]
+    packed = (golden / "ndjsonFiles" / "oneline_second_nuc.json.zst").read_bytes()
+    buffer = ctypes.create_string_buffer(1 << 20)
+    n_bytes = zstd.ZSTD_decompress(buffer, len(buffer), packed, len(packed))
+    text = buffer.raw[:n_bytes].decode()
+    assert '"\n    "testSecondSequence"' in text
+    repaired = tmp_path / "oneline_second_nuc_repaired.json"
+    repaired.write_text(text.replace('"\n    "testSecondSequence"', '",\n    "testSecondSequence"'))
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.Database.from_directory(directory("too_many_in_json_repaired", repaired, thousand / "reference_genomes.json"))
+    assert "The aligned nucleotide sequence testSecondSequence which is contained in the input file" in str(err.value) and "is not contained in the reference sequences." in str(err.value)
+    with pytest.raises(pysilo.SiloError) as err:
+        pysilo.Database.from_directory(directory("too_few_genes", golden / "ndjsonFiles" / "oneline_without_ORF.json.zst", thousand / "reference_genomes.json"))
+    assert "The aligned amino acid sequence ORF" in str(err.value) and "which is contained in the reference sequences is not contained in the input file" in str(err.value)
