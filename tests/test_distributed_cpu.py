@@ -133,6 +133,10 @@ def test_row_sliced_shards_add_up_to_the_whole_database(libs, world):
     want_table, produced = oracle.mutation_counts(whole, query, "main", 16 * genome)
     want_count = oracle.execute(whole, {"action": {"type": "Aggregated"}, "filterExpression": flt})[0]["count"]
     assert produced and want_count > 0
+    grouped = {"action": {"type": "Aggregated", "groupByFields": ["region", "pangoLineage", "age"], "orderByFields": [{"field": "count", "order": "descending"}, "pangoLineage", "region", "age"], "limit": 25},
+               "filterExpression": flt}
+    partial_query = {"action": {"type": "Aggregated", "groupByFields": ["region", "pangoLineage", "age"]}, "filterExpression": flt}
+    partials = []
     table, count, rows, loads = np.zeros(16 * genome, dtype=np.uint64), 0, 0, []
     for rank in range(world):
         shard = pysilo.Database.synthetic(n_rows, SEED, genome_length=genome, world=world, rank=rank, row_slices=world)
@@ -140,9 +144,11 @@ def test_row_sliced_shards_add_up_to_the_whole_database(libs, world):
         local, _ = oracle.mutation_counts_subset(shard, query, "main", 16 * genome, shard.owned)
         table += local
         count += sum(oracle.filter_cardinality(shard, flt, p) for p in shard.owned)
+        partials.append(oracle.execute_subset_text(shard, partial_query, shard.owned))      # what Engine.execute_partial sends to rank 0
         loads.append(sum(shard.partition_rows(p) for p in shard.owned))
         rows += loads[-1]
         shard.close()
     assert rows == n_rows and max(loads) - min(loads) <= whole.n_partitions      # slices differ by at most one row per lineage
     assert count == want_count
     assert np.array_equal(table, want_table.astype(np.uint64))
+    assert pysilo.merge_partials(whole, grouped, partials) == oracle.execute(whole, grouped)      # grouped Aggregated: partial tuples add up
