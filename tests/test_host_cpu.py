@@ -17,6 +17,16 @@ def test_abi_exports_every_declared_symbol(libs):
         assert hasattr(lib, name), f"libsilo_b200.so does not export {name}"
 
 
+def test_header_is_plain_c(tmp_path):
+    """the drop-in boundary is a C ABI: include/silo_b200.h compiles as C99 with pedantic warnings as errors, no C++ in the signatures"""
+    import subprocess
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    source = tmp_path / "abi.c"
+    source.write_text('#include "silo_b200.h"\nint main(void) { sb_node node; sb_mutation_row row; sb_group_row group; (void)node; (void)row; (void)group; return 0; }\n')
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-I", str(root / "include"), str(source)], check=True)
+
+
 def test_no_cpu_fallback_without_gpu(libs):
     import torch
     if torch.cuda.is_available():
