@@ -27,6 +27,18 @@ def test_header_is_plain_c(tmp_path):
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-I", str(root / "include"), str(source)], check=True)
 
 
+def test_integration_snippets_compile_and_link(libs, tmp_path):
+    """the calls INTEGRATION.md shows (tests/integration_snippets.cpp) compile against the header with warnings as errors and link against
+    libsilo_b200.so -- the document cannot drift from the ABI"""
+    import subprocess
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    binary = tmp_path / "integration_snippets"
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I", str(root / "include"), str(root / "tests" / "integration_snippets.cpp"), "-o", str(binary),
+                    "-L", str(root / "lapis-silo_b200"), "-lsilo_b200", f"-Wl,-rpath,{root / 'lapis-silo_b200'}"], check=True)
+    assert subprocess.run([str(binary)], check=True, capture_output=True, text=True).stdout.strip() == "links"
+
+
 def test_no_cpu_fallback_without_gpu(libs):
     import torch
     if torch.cuda.is_available():
